@@ -1,0 +1,164 @@
+/* particles_cuda.h — C ABI of libparticles_cuda, the B200 (sm_100a) replacement for the
+ * per-frame particle step of J-A-G-A-N/Particle-Simulator (src/core.zig).
+ *
+ * The reference has no FFI of its own: its boundary is the Zig API of src/core.zig as
+ * main.zig consumes it (src/main.zig:9-13,63-75,102-109,124).  Every entry point below
+ * names the reference item it stands in for (file:line into /root/reference).  The Zig
+ * shim that keeps core.zig's type and method names over this ABI is zig/core_cuda.zig;
+ * the C++ mirror used by the headless driver is host/core_cuda.hpp (both inside the
+ * package directory); INTEGRATION.md shows the build.zig change.
+ *
+ * Conventions
+ *   - plain C types only; every function returns a ps_status (0 = ok, < 0 = error)
+ *     unless stated; nothing aborts inside the library.
+ *   - host arrays are interleaved (x,y) pairs, byte-identical to Zig's []@Vector(2,f64)
+ *     (src/core.zig:5,14-16); they stay owned by the caller.
+ *   - one handle = one owner thread.  ps_step* are stream-ordered and return before the
+ *     GPU finishes; ps_download*, ps_contact_pairs, ps_get_stats and ps_sync wait.
+ *   - particle identity is the array index (src/core.zig:411-417, src/main.zig:103):
+ *     downloads are always in original index order.
+ *   - there is no CPU fallback: without a usable CUDA device ps_create fails with
+ *     PS_ERR_NO_DEVICE.
+ */
+#ifndef PARTICLES_CUDA_H
+#define PARTICLES_CUDA_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PS_ABI_VERSION 1
+
+typedef struct ps_sim ps_sim; /* opaque: Particles + Solver + SpatialHashGrid state on one GPU */
+
+typedef enum ps_status {
+    PS_OK = 0,
+    PS_ERR_BAD_ARG = -1,       /* null pointer, zero grid, size mismatch, ... */
+    PS_ERR_OOM = -2,           /* device or pinned-host allocation failed (Zig: error.OutOfMemory, src/core.zig:23-26,76-79) */
+    PS_ERR_CUDA = -3,          /* any other CUDA runtime error; text in ps_last_error */
+    PS_ERR_NCCL = -4,          /* reserved for the multi-GPU slab path */
+    PS_ERR_CELL_OVERFLOW = -5, /* a grid cell held > 255 particles: the reference's u8 counter would wrap or panic (src/core.zig:51,132) */
+    PS_ERR_CAPACITY = -6,      /* contact list larger than the configured capacity; state is left at the failing sub-step's post-bounce point */
+    PS_ERR_NO_DEVICE = -7      /* no CUDA device / library built without one: the product has no CPU path */
+} ps_status;
+
+typedef enum ps_precision {
+    PS_F64 = 0, /* core.zig as written (Vec2f64, src/core.zig:5) */
+    PS_F32 = 1  /* same operation order, every f64 replaced by f32 (north_star's fp32 SoA layout) */
+} ps_precision;
+
+/* Scene description = the arguments main.zig passes to Particles.init, Solver.init,
+ * SpatialHashGrid.init and updatePhysics (src/main.zig:63-75,109).  Zero-initialise, set
+ * struct_size = sizeof(ps_config), then fill. */
+typedef struct ps_config {
+    uint32_t struct_size;
+    int32_t  device;            /* CUDA device ordinal */
+    uint64_t count;             /* Particles.init particles_count       src/core.zig:22   (main.zig: 13 000) */
+    double   radius;            /* Particles.init radius                src/core.zig:22   (2.0) */
+    double   width, height;     /* updatePhysics width/height           src/core.zig:245  (720, 640); also SpatialHashGrid.init :60 */
+    double   grid_size;         /* SpatialHashGrid.init grid_size       src/core.zig:60   (2*radius = 4.0) */
+    double   target_fps;        /* Solver.init target_fps               src/core.zig:226  (60) */
+    uint64_t sub_steps;         /* Solver.init sub_steps                                  (8) */
+    double   g;                 /* Solver.init g                                          (50) */
+    double   boundary_damping;  /* Solver.init boundary_damping                           (0.1) */
+    double   particle_damping;  /* Solver.init particle_damping                           (0.9) */
+    int32_t  precision;         /* ps_precision */
+    int32_t  collisions;        /* 1 = faithful updatePhysics (src/core.zig:262-266 run every sub-step);
+                                   0 = integrate + wall bounce only (stop after :261) — the mode
+                                   BASELINE.json's integration configs name; the reference has no such switch */
+    uint32_t fuse_substeps;     /* integrate-only scenes: advance up to this many sub-steps per kernel pass in
+                                   registers (bit-identical; 0 or 1 = one pass per sub-step, the roofline run) */
+    uint32_t contacts_per_particle; /* capacity of the contact list, entries per particle (0 = default 12) */
+    uint64_t reserved[4];
+} ps_config;
+
+typedef struct ps_stats {
+    uint64_t substeps_done;     /* sub-steps completed since ps_create */
+    uint64_t pairs_last;        /* collision_pairs.items.len of the last sub-step (src/core.zig:211) */
+    uint64_t pairs_total;       /* summed over all sub-steps */
+    uint64_t rounds_last;       /* parallel rounds the ordered resolve needed in the last sub-step */
+    uint64_t rounds_total;
+    uint32_t max_cell_count;    /* largest cell population seen (reference limit 255) */
+    uint32_t reserved;
+    uint64_t kernel_launches;   /* CUDA kernels this handle has launched since ps_create (host-side count) */
+} ps_stats;
+
+/* ---- lifetime ----------------------------------------------------------------------- */
+
+/* Particles.init (src/core.zig:22-39) + Solver.init (:226-238) + SpatialHashGrid.init
+ * (:60-85) on device cfg->device.  Positions, velocities and accelerations start at zero
+ * (:27-29); gravity starts off (t_acc = false, :220). */
+int ps_create(const ps_config* cfg, ps_sim** out);
+
+/* Particles.deinit (src/core.zig:41-44) + SpatialHashGrid.deinit (:87-93). NULL is ignored. */
+void ps_destroy(ps_sim* sim);
+
+/* ---- state in / out --------------------------------------------------------------------
+ * Stand in for direct access to particles.positions / .velocities (src/core.zig:14-15),
+ * which Spawner.spawnRandom writes (:403-408) and main.zig reads every frame (:102-107). */
+int ps_upload(ps_sim* sim, const double* pos_xy, const double* vel_xy);      /* 2*count doubles each */
+int ps_upload_f32(ps_sim* sim, const float* pos_xy, const float* vel_xy);
+int ps_download(ps_sim* sim, double* pos_xy, double* vel_xy);                /* either may be NULL */
+int ps_download_f32(ps_sim* sim, float* pos_xy, float* vel_xy);              /* pos = the GUI's @floatCast, src/main.zig:104-105 */
+/* particles.accelerations (src/core.zig:16): a pure function of t_acc and g (:249-257). */
+int ps_download_acc(ps_sim* sim, double* acc_xy);
+
+/* ---- stepping ----------------------------------------------------------------------- */
+
+/* Solver.updatePhysics (src/core.zig:245-268) called `frames` times = frames*sub_steps sub-steps. */
+int ps_step(ps_sim* sim, uint64_t frames);
+/* `substeps` iterations of the loop body at src/core.zig:247-267 (benchmarks count sub-steps). */
+int ps_step_substeps(ps_sim* sim, uint64_t substeps);
+/* Solver.toggle_acc (src/core.zig:239-241): flips gravity and the collision response mode. */
+int ps_toggle_acc(ps_sim* sim);
+int ps_set_acc(ps_sim* sim, int on);
+int ps_get_acc(const ps_sim* sim);   /* returns 0/1, or < 0 on NULL */
+
+/* Wait for all queued work; returns any deferred device-side error (cell overflow, capacity). */
+int ps_sync(ps_sim* sim);
+/* Queue work on the caller's cudaStream_t instead of the handle's own stream (NULL = back to own). */
+int ps_set_stream(ps_sim* sim, void* cuda_stream);
+
+/* ---- inspection --------------------------------------------------------------------- */
+
+/* SpatialHashGrid.rows / .cols as init derives them (src/core.zig:61-67). */
+int ps_grid_shape(const ps_sim* sim, uint64_t* rows, uint64_t* cols);
+/* Solver.dt (src/core.zig:228) widened to double. */
+double ps_dt(const ps_sim* sim);
+/* Ask for shg.collision_pairs (src/core.zig:55,203) of every following sub-step to be kept. */
+int ps_capture_pairs(ps_sim* sim, int on);
+/* The ordered list {particle_i, particle_j} of the last sub-step, reference order
+ * (src/core.zig:164-209).  Copies min(cap, count) entries (2 uint64 each); *count = full length. */
+int ps_contact_pairs(ps_sim* sim, uint64_t* out_pairs, uint64_t cap, uint64_t* count);
+int ps_get_stats(ps_sim* sim, ps_stats* out);
+/* Raw device pointers of the structure-of-arrays state (element type per cfg.precision), in
+ * original index order, valid until ps_destroy; for callers that keep data on the GPU. */
+int ps_device_state(ps_sim* sim, void** px, void** py, void** vx, void** vy);
+
+/* ---- errors / misc ------------------------------------------------------------------ */
+
+const char* ps_last_error(const ps_sim* sim); /* sim may be NULL: last ps_create failure on this thread */
+const char* ps_status_string(int status);
+int ps_abi_version(void);
+
+/* Pinned host memory for the caller's position/velocity slices, so that uploads and the
+ * per-frame read-back run at PCIe speed (std.heap.c_allocator's role, src/main.zig:47). */
+int ps_host_alloc(void** ptr, uint64_t bytes);
+int ps_host_free(void* ptr);
+
+/* ---- kernels on caller-owned device memory -------------------------------------------
+ * The integrate loop (src/core.zig:248-260) fused with _applyBoundary (:290-318) for
+ * `substeps` sub-steps on SoA device arrays of `count` elements each (16-byte aligned,
+ * padded to a multiple of 4 elements), queued on `cuda_stream`.  `cfg` supplies radius,
+ * width, height, fps, sub_steps, g and damping; t_acc is the gravity flag. */
+int ps_integrate_bounce_f32(const ps_config* cfg, int t_acc, float* px, float* py, float* vx, float* vy,
+                            uint64_t count, uint64_t substeps, void* cuda_stream);
+int ps_integrate_bounce_f64(const ps_config* cfg, int t_acc, double* px, double* py, double* vx, double* vy,
+                            uint64_t count, uint64_t substeps, void* cuda_stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PARTICLES_CUDA_H */

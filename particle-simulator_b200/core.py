@@ -1,0 +1,329 @@
+"""Host-side mirror of src/core.zig's public API over the C ABI.
+
+Same type and method names as the reference (``Particles``, ``SpatialHashGrid``, ``Solver``,
+``Spawner``; ``updatePhysics``, ``toggle_acc``, ``spawnRandom``) so that a caller written
+against core.zig — main.zig's init / updateAndRender (src/main.zig:35-76,95-114) — reads the
+same.  All arithmetic happens in libparticles_cuda on the GPU; this file only moves arguments.
+
+Differences a caller sees (documented in INTEGRATION.md):
+  * ``Particles.positions`` / ``.velocities`` are host mirrors ((n, 2) float64, the layout of
+    ``[]@Vector(2, f64)``).  ``Solver.updatePhysics`` refreshes ``positions`` after every call
+    when ``read_back="frame"`` (what the GUI needs, src/main.zig:102-107); with
+    ``read_back="never"`` (headless) call ``Particles.sync_host()`` when you want them.
+  * writing into the host mirrors must be followed by ``Particles.mark_dirty()`` (Spawner does it).
+  * ``SpatialHashGrid`` holds parameters only; its scratch arrays live on the device.
+"""
+from __future__ import annotations
+
+import ctypes
+
+import numpy as np
+
+from . import capi, scenes
+
+
+def _check(rc: int, handle=None) -> None:
+    if rc != capi.PS_OK:
+        L = capi.load()
+        text = L.ps_last_error(handle) or L.ps_status_string(rc) or b""
+        raise capi.PsError(rc, text.decode("utf-8", "replace"))
+
+
+class Particles:
+    """src/core.zig:13-45."""
+
+    def __init__(self, particles_count: int, radius: float):
+        self.positions = np.zeros((particles_count, 2), dtype=np.float64)      # :27
+        self.velocities = np.zeros((particles_count, 2), dtype=np.float64)     # :28
+        self.accelerations = np.zeros((particles_count, 2), dtype=np.float64)  # :29
+        self.colors = np.zeros((particles_count, 4), dtype=np.uint8)           # sdl.Color r,g,b,a  :17
+        self.radius = float(radius)
+        self._dirty = True      # host mirrors newer than device state
+        self._sim = None        # Simulation bound by Solver.updatePhysics
+
+    @classmethod
+    def init(cls, particles_count: int, radius: float) -> "Particles":
+        return cls(particles_count, radius)
+
+    def __len__(self) -> int:
+        return self.positions.shape[0]
+
+    def mark_dirty(self) -> None:
+        self._dirty = True
+
+    def sync_host(self, velocities: bool = True) -> None:
+        """Copy the device state back into the host mirrors."""
+        if self._sim is not None and not self._dirty:
+            self._sim.download(self.positions, self.velocities if velocities else None)
+            self._sim.download_acc(self.accelerations)
+
+    def deinit(self) -> None:  # :41-44
+        if self._sim is not None:
+            self._sim.close()
+            self._sim = None
+
+
+class SpatialHashGrid:
+    """src/core.zig:47-93 — parameters only; rows/cols derived as init does (:61-67)."""
+
+    def __init__(self, width: float, height: float, grid_size: float, particles_count: int):
+        self.width = float(width)
+        self.height = float(height)
+        self.grid_size = float(grid_size)
+        self.particles_count = int(particles_count)
+        w, h, gs = int(width), int(height), int(grid_size)
+        if gs <= 0:
+            raise ValueError("grid_size truncates to <= 0 (src/core.zig:63)")
+        self.cols = w // gs
+        self.rows = h // gs
+
+    @classmethod
+    def init(cls, width, height, grid_size, particles_count) -> "SpatialHashGrid":
+        return cls(width, height, grid_size, particles_count)
+
+    def deinit(self) -> None:
+        pass
+
+
+class Simulation:
+    """Thin RAII wrapper of one ps_sim handle (one GPU)."""
+
+    def __init__(self, scene: scenes.Scene, *, precision: str = "f64", collisions: bool = True, device: int = 0,
+                 fuse_substeps: int = 0, contacts_per_particle: int = 0):
+        self._L = capi.load()
+        cfg = capi.PsConfig()
+        cfg.struct_size = ctypes.sizeof(capi.PsConfig)
+        cfg.device = device
+        cfg.count = scene.count
+        cfg.radius = scene.radius
+        cfg.width = scene.width
+        cfg.height = scene.height
+        cfg.grid_size = scene.grid_size
+        cfg.target_fps = scene.target_fps
+        cfg.sub_steps = scene.sub_steps
+        cfg.g = scene.g
+        cfg.boundary_damping = scene.boundary_damping
+        cfg.particle_damping = scene.particle_damping
+        cfg.precision = capi.PS_F64 if precision == "f64" else capi.PS_F32
+        cfg.collisions = 1 if collisions else 0
+        cfg.fuse_substeps = fuse_substeps
+        cfg.contacts_per_particle = contacts_per_particle
+        self.cfg = cfg
+        self.scene = scene
+        self.precision = precision
+        self.count = scene.count
+        h = ctypes.c_void_p()
+        rc = self._L.ps_create(ctypes.byref(cfg), ctypes.byref(h))
+        if rc != capi.PS_OK:
+            raise capi.PsError(rc, (self._L.ps_last_error(None) or b"").decode())
+        self._h = h
+
+    # -- lifetime
+    def close(self) -> None:
+        if getattr(self, "_h", None):
+            self._L.ps_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    # -- state
+    @staticmethod
+    def _ptr(a):
+        return None if a is None else ctypes.c_void_p(a.ctypes.data if isinstance(a, np.ndarray) else int(a))
+
+    def upload(self, pos, vel) -> None:
+        """pos/vel: C-contiguous (n, 2) float64 or float32 arrays (or None)."""
+        for a in (pos, vel):
+            if a is not None:
+                assert a.flags.c_contiguous and a.shape == (self.count, 2), "expected a C-contiguous (count, 2) array"
+        ref = pos if pos is not None else vel
+        fn = self._L.ps_upload if ref.dtype == np.float64 else self._L.ps_upload_f32
+        assert ref.dtype in (np.float64, np.float32)
+        _check(fn(self._h, self._ptr(pos), self._ptr(vel)), self._h)
+
+    def download(self, pos=None, vel=None, dtype=np.float64):
+        """Fill (or allocate) interleaved (n, 2) arrays in original index order."""
+        if pos is None and vel is None:
+            pos = np.empty((self.count, 2), dtype=dtype)
+            vel = np.empty((self.count, 2), dtype=dtype)
+        ref = pos if pos is not None else vel
+        fn = self._L.ps_download if ref.dtype == np.float64 else self._L.ps_download_f32
+        _check(fn(self._h, self._ptr(pos), self._ptr(vel)), self._h)
+        return pos, vel
+
+    def download_acc(self, acc=None):
+        if acc is None:
+            acc = np.empty((self.count, 2), dtype=np.float64)
+        _check(self._L.ps_download_acc(self._h, self._ptr(acc)), self._h)
+        return acc
+
+    # -- stepping
+    def step(self, frames: int = 1) -> None:
+        _check(self._L.ps_step(self._h, frames), self._h)
+
+    def step_substeps(self, substeps: int) -> None:
+        _check(self._L.ps_step_substeps(self._h, substeps), self._h)
+
+    def toggle_acc(self) -> None:
+        _check(self._L.ps_toggle_acc(self._h), self._h)
+
+    def set_acc(self, on: bool) -> None:
+        _check(self._L.ps_set_acc(self._h, int(on)), self._h)
+
+    @property
+    def t_acc(self) -> bool:
+        return self._L.ps_get_acc(self._h) == 1
+
+    def sync(self) -> None:
+        _check(self._L.ps_sync(self._h), self._h)
+
+    def set_stream(self, cuda_stream: int | None) -> None:
+        _check(self._L.ps_set_stream(self._h, ctypes.c_void_p(cuda_stream or 0)), self._h)
+
+    # -- inspection
+    def grid_shape(self):
+        r, c = ctypes.c_uint64(), ctypes.c_uint64()
+        _check(self._L.ps_grid_shape(self._h, ctypes.byref(r), ctypes.byref(c)), self._h)
+        return int(r.value), int(c.value)
+
+    @property
+    def dt(self) -> float:
+        return float(self._L.ps_dt(self._h))
+
+    def capture_pairs(self, on: bool = True) -> None:
+        _check(self._L.ps_capture_pairs(self._h, int(on)), self._h)
+
+    def contact_pairs(self) -> np.ndarray:
+        """Ordered (m, 2) uint64 array {particle_i, particle_j} of the last sub-step."""
+        cnt = ctypes.c_uint64()
+        _check(self._L.ps_contact_pairs(self._h, None, 0, ctypes.byref(cnt)), self._h)
+        out = np.empty((int(cnt.value), 2), dtype=np.uint64)
+        if cnt.value:
+            _check(self._L.ps_contact_pairs(self._h, self._ptr(out), cnt.value, ctypes.byref(cnt)), self._h)
+        return out
+
+    def stats(self) -> dict:
+        s = capi.PsStats()
+        _check(self._L.ps_get_stats(self._h, ctypes.byref(s)), self._h)
+        return {k: int(getattr(s, k)) for k, _ in capi.PsStats._fields_ if k != "reserved"}
+
+    def device_state(self):
+        """Raw device pointers (px, py, vx, vy) of the SoA state."""
+        p = [ctypes.c_void_p() for _ in range(4)]
+        _check(self._L.ps_device_state(self._h, *[ctypes.byref(x) for x in p]), self._h)
+        return tuple(int(x.value or 0) for x in p)
+
+    def debug_set_integrate_variant(self, variant: int) -> None:
+        _check(self._L.ps_debug_set_integrate_variant(self._h, variant), self._h)
+
+    def debug_set_transfer_mode(self, mode: int) -> None:
+        """0 = kernels read/write pinned host buffers directly; 1 = always DMA through device staging."""
+        _check(self._L.ps_debug_set_transfer_mode(self._h, mode), self._h)
+
+
+class Solver:
+    """src/core.zig:217-268."""
+
+    def __init__(self, target_fps: float, sub_steps: int, g: float, boundary_damping: float, particle_damping: float, *,
+                 precision: str = "f64", collisions: bool = True, device: int = 0, read_back: str = "frame"):
+        self.delta_time = 1.0 / target_fps                 # :227
+        self.dt = self.delta_time / float(sub_steps)       # :228
+        self.target_fps = float(target_fps)
+        self.sub_steps = int(sub_steps)
+        self.g = float(g)
+        self.boundary_damping = float(boundary_damping)
+        self.particle_damping = float(particle_damping)
+        self.t_acc = False                                 # :220
+        self.precision = precision
+        self.collisions = collisions
+        self.device = device
+        self.read_back = read_back
+
+    @classmethod
+    def init(cls, target_fps, sub_steps, g, boundary_damping, particle_damping, **kw) -> "Solver":
+        return cls(target_fps, sub_steps, g, boundary_damping, particle_damping, **kw)
+
+    def toggle_acc(self) -> None:                          # :239-241
+        self.t_acc = not self.t_acc
+
+    def _bind(self, particles: Particles, width: float, height: float, shg: SpatialHashGrid) -> Simulation:
+        scene = scenes.Scene(count=len(particles), radius=particles.radius, width=float(width), height=float(height),
+                             grid_size=shg.grid_size, target_fps=self.target_fps, sub_steps=self.sub_steps, g=self.g,
+                             boundary_damping=self.boundary_damping, particle_damping=self.particle_damping)
+        sim = particles._sim
+        if sim is None or sim.scene != scene or sim.precision != self.precision:
+            if sim is not None:
+                particles.sync_host()
+                sim.close()
+                particles._dirty = True
+            sim = Simulation(scene, precision=self.precision, collisions=self.collisions, device=self.device)
+            particles._sim = sim
+        return sim
+
+    def updatePhysics(self, particles: Particles, width: float, height: float, shg: SpatialHashGrid) -> None:
+        """src/core.zig:245-268: sub_steps x (integrate, _applyBoundary, grid build, detect, resolve)."""
+        sim = self._bind(particles, width, height, shg)
+        if particles._dirty:
+            sim.upload(particles.positions, particles.velocities)
+            particles._dirty = False
+        sim.set_acc(self.t_acc)
+        sim.step(1)
+        if self.read_back == "frame":
+            sim.download(particles.positions, None)
+
+    update_physics = updatePhysics
+
+
+def hsv_to_rgba(h: np.ndarray, s: float, v: float, a: int) -> np.ndarray:
+    """colors.zig hsvToSdlColor (src/colors.zig:6-47) in float32, vectorised over h."""
+    h = h.astype(np.float32)
+    c = np.float32(v) * np.float32(s)
+    x = c * (np.float32(1.0) - np.abs(np.mod(h / np.float32(60.0), np.float32(2.0)) - np.float32(1.0)))
+    m = np.float32(v) - c
+    z = np.zeros_like(h)
+    cc = np.full_like(h, c)
+    sector = np.minimum((h // np.float32(60.0)).astype(np.int64), 5)
+    r = np.choose(sector, [cc, x, z, z, x, cc])
+    g = np.choose(sector, [x, cc, cc, x, z, z])
+    b = np.choose(sector, [z, z, x, cc, cc, x])
+    out = np.empty(h.shape + (4,), dtype=np.uint8)
+    out[..., 0] = ((r + m) * np.float32(255.0)).astype(np.uint8)
+    out[..., 1] = ((g + m) * np.float32(255.0)).astype(np.uint8)
+    out[..., 2] = ((b + m) * np.float32(255.0)).astype(np.uint8)
+    out[..., 3] = a
+    return out
+
+
+class Spawner:
+    """src/core.zig:394-418.  `rng` is an integer seed: the reference's std.Random stream is
+    not reproduced (its seed is the wall clock, src/main.zig:45); the distribution is."""
+
+    @staticmethod
+    def spawnRandom(par: Particles, rng: int, width: float, height: float, vmin: float, vmax: float) -> None:
+        scene = scenes.Scene(count=len(par), radius=par.radius, width=float(width), height=float(height),
+                             vel_min=float(vmin), vel_max=float(vmax))
+        pos, vel = scenes.spawn(scene, seed=int(rng))
+        par.positions[:] = pos
+        par.velocities[:] = vel
+        par.mark_dirty()
+        Spawner.assignRainbowColors(par)
+
+    @staticmethod
+    def assignRainbowColors(par: Particles) -> None:      # :411-417
+        n = len(par)
+        if n == 0:
+            return
+        hue = np.arange(n, dtype=np.float32) / np.float32(n) * np.float32(360.0)
+        par.colors[:] = hsv_to_rgba(hue, 1.0, 1.0, 255)
+
+    spawn_random = spawnRandom

@@ -1,0 +1,414 @@
+// ps_api.cu — the C ABI of libparticles_cuda (include/particles_cuda.h).
+//
+// One ps_sim = the reference's Particles + Solver + SpatialHashGrid (src/core.zig:13-45,
+// 47-93, 217-238) living on one B200.  No CPU path exists in this library: every entry
+// point that computes launches CUDA kernels, and ps_create fails without a device.
+#include <cuda_runtime.h>
+
+#include <cstring>
+#include <memory>
+#include <new>
+#include <string>
+
+#include "particles_cuda.h"
+#include "ps_collide.cuh"
+#include "ps_common.cuh"
+#include "ps_integrate.cuh"
+#include "ps_transfer.cuh"
+
+using ps::Error;
+
+static thread_local std::string g_create_error;
+
+struct ps_sim {
+    ps_config cfg{};
+    Error err;
+    int device = 0;
+    bool t_acc = false;            // Solver.t_acc, src/core.zig:220
+    bool stepped_with_acc = false; // what particles.accelerations currently holds (Q6)
+    uint64_t n = 0, n_pad = 0;
+    uint32_t rows = 0, cols = 0;
+    cudaStream_t own_stream = nullptr, stream = nullptr;
+    void* stage = nullptr;         // device staging for pageable host buffers
+    uint64_t stage_bytes = 0;
+    uint64_t substeps_done = 0;
+    int integrate_variant = 0;
+    int transfer_mode = 0;         // 0: kernels address pinned host buffers directly; 1: always DMA via staging
+    uint64_t launches = 0;         // kernels launched by this handle
+
+    virtual ~ps_sim() {}
+    virtual int upload(const void* pos, const void* vel, bool host_f64) = 0;
+    virtual int download(void* pos, void* vel, bool host_f64) = 0;
+    virtual int step(uint64_t substeps) = 0;
+    virtual int device_state(void** px, void** py, void** vx, void** vy) = 0;
+    virtual int contact_pairs(uint64_t* out, uint64_t cap, uint64_t* count) = 0;
+    virtual int capture_pairs(bool on) = 0;
+    virtual int stats(ps_stats* out) = 0;
+    virtual int check_deferred() = 0;
+    virtual double dt() const = 0;
+
+    int ensure_stage(uint64_t bytes) {
+        if (bytes <= stage_bytes) return PS_OK;
+        if (stage) { cudaFree(stage); stage = nullptr; stage_bytes = 0; }
+        PS_CUDA_TRY(err, cudaMalloc(&stage, bytes));
+        stage_bytes = bytes;
+        return PS_OK;
+    }
+    int fail(int status, const std::string& text) { err.status = status; err.text = text; return status; }
+};
+
+namespace {
+
+struct DeviceGuard {
+    int prev = -1;
+    explicit DeviceGuard(int dev) { cudaGetDevice(&prev); if (prev != dev) cudaSetDevice(dev); else prev = -1; }
+    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
+template <class Real>
+struct SimT final : ps_sim {
+    Real *px = nullptr, *py = nullptr, *vx = nullptr, *vy = nullptr;
+    ps::Collider<Real> col;
+
+    ~SimT() override {
+        DeviceGuard g(device);
+        if (own_stream) cudaStreamSynchronize(own_stream);
+        col.destroy();
+        cudaFree(px); cudaFree(py); cudaFree(vx); cudaFree(vy);
+        cudaFree(stage);
+        if (own_stream) cudaStreamDestroy(own_stream);
+    }
+
+    int init() {
+        DeviceGuard g(device);
+        PS_CUDA_TRY(err, cudaStreamCreateWithFlags(&own_stream, cudaStreamNonBlocking));
+        stream = own_stream;
+        n_pad = ps::round_up(n ? n : 1, 4);
+        const size_t bytes = n_pad * sizeof(Real);
+        PS_CUDA_TRY(err, cudaMalloc(&px, bytes));
+        PS_CUDA_TRY(err, cudaMalloc(&py, bytes));
+        PS_CUDA_TRY(err, cudaMalloc(&vx, bytes));
+        PS_CUDA_TRY(err, cudaMalloc(&vy, bytes));
+        // Particles.init zero-fills (src/core.zig:27-29)
+        PS_CUDA_TRY(err, cudaMemsetAsync(px, 0, bytes, stream));
+        PS_CUDA_TRY(err, cudaMemsetAsync(py, 0, bytes, stream));
+        PS_CUDA_TRY(err, cudaMemsetAsync(vx, 0, bytes, stream));
+        PS_CUDA_TRY(err, cudaMemsetAsync(vy, 0, bytes, stream));
+        if (cfg.collisions) {
+            const int rc = col.create(cfg, n, rows, cols, stream, err);
+            if (rc != PS_OK) return rc;
+        }
+        PS_CUDA_TRY(err, cudaStreamSynchronize(stream));
+        return PS_OK;
+    }
+
+    template <class H>
+    int upload_one(const H* host_xy, Real* ax, Real* ay) {
+        using HP = typename ps::Pair<H>::type;
+        void* alias = nullptr;
+        const HP* src;
+        if (transfer_mode == 0 && ps::host_ptr_is_pinned(host_xy, &alias)) {
+            src = reinterpret_cast<const HP*>(alias);
+        } else {
+            const uint64_t bytes = n * sizeof(HP);
+            const int rc = ensure_stage(bytes);
+            if (rc != PS_OK) return rc;
+            PS_CUDA_TRY(err, cudaMemcpyAsync(stage, host_xy, bytes, cudaMemcpyHostToDevice, stream));
+            src = reinterpret_cast<const HP*>(stage);
+        }
+        ps::deinterleave_kernel<H, Real><<<ps::transfer_grid(n), 256, 0, stream>>>(src, ax, ay, n);
+        ++launches;
+        PS_CUDA_TRY(err, cudaGetLastError());
+        return PS_OK;
+    }
+
+    int upload(const void* pos, const void* vel, bool host_f64) override {
+        DeviceGuard g(device);
+        if (n == 0) return PS_OK;
+        int rc = PS_OK;
+        if (pos) rc = host_f64 ? upload_one((const double*)pos, px, py) : upload_one((const float*)pos, px, py);
+        if (rc != PS_OK) return rc;
+        if (vel) rc = host_f64 ? upload_one((const double*)vel, vx, vy) : upload_one((const float*)vel, vx, vy);
+        if (rc != PS_OK) return rc;
+        // the caller may reuse or free its buffers as soon as we return
+        PS_CUDA_TRY(err, cudaStreamSynchronize(stream));
+        return PS_OK;
+    }
+
+    template <class H>
+    int download_one(H* host_xy, const Real* ax, const Real* ay) {
+        using HP = typename ps::Pair<H>::type;
+        void* alias = nullptr;
+        ++launches;
+        if (transfer_mode == 0 && ps::host_ptr_is_pinned(host_xy, &alias)) {
+            ps::interleave_kernel<Real, H><<<ps::transfer_grid(n), 256, 0, stream>>>(ax, ay, reinterpret_cast<HP*>(alias), n);
+            PS_CUDA_TRY(err, cudaGetLastError());
+        } else {
+            const uint64_t bytes = n * sizeof(HP);
+            const int rc = ensure_stage(bytes);
+            if (rc != PS_OK) return rc;
+            ps::interleave_kernel<Real, H><<<ps::transfer_grid(n), 256, 0, stream>>>(ax, ay, reinterpret_cast<HP*>(stage), n);
+            PS_CUDA_TRY(err, cudaGetLastError());
+            PS_CUDA_TRY(err, cudaMemcpyAsync(host_xy, stage, bytes, cudaMemcpyDeviceToHost, stream));
+            // wait before `stage` is reused by the next array
+            PS_CUDA_TRY(err, cudaStreamSynchronize(stream));
+        }
+        return PS_OK;
+    }
+
+    int download(void* pos, void* vel, bool host_f64) override {
+        DeviceGuard g(device);
+        int rc = PS_OK;
+        if (n) {
+            if (pos) rc = host_f64 ? download_one((double*)pos, px, py) : download_one((float*)pos, px, py);
+            if (rc != PS_OK) return rc;
+            if (vel) rc = host_f64 ? download_one((double*)vel, vx, vy) : download_one((float*)vel, vx, vy);
+            if (rc != PS_OK) return rc;
+        }
+        PS_CUDA_TRY(err, cudaStreamSynchronize(stream));
+        return check_deferred();
+    }
+
+    int step(uint64_t substeps) override {
+        DeviceGuard g(device);
+        if (err.status != PS_OK && err.status != PS_ERR_BAD_ARG) return err.status;   // sticky device-side failure
+        const ps::StepConst<Real> k = ps::make_step_const<Real>(cfg, t_acc, rows, cols);
+        if (substeps) stepped_with_acc = t_acc;
+        if (!cfg.collisions) {
+            const uint64_t fuse = cfg.fuse_substeps > 1 ? cfg.fuse_substeps : 1;
+            uint64_t left = substeps;
+            while (left) {
+                const uint64_t now = left < fuse ? left : fuse;
+                PS_CUDA_TRY(err, ps::launch_integrate_bounce<Real>(px, py, vx, vy, n_pad, k, (int)now, integrate_variant, stream));
+                ++launches;
+                left -= now;
+            }
+        } else {
+            for (uint64_t s = 0; s < substeps; ++s) {
+                const int rc = col.substep(px, py, vx, vy, k, stream, err, &launches);
+                if (rc != PS_OK) return rc;
+            }
+        }
+        substeps_done += substeps;
+        return PS_OK;
+    }
+
+    int device_state(void** ox, void** oy, void** ovx, void** ovy) override {
+        if (ox) *ox = px; if (oy) *oy = py; if (ovx) *ovx = vx; if (ovy) *ovy = vy;
+        return PS_OK;
+    }
+
+    int capture_pairs(bool on) override {
+        if (!cfg.collisions) return fail(PS_ERR_BAD_ARG, "ps_capture_pairs: handle was created with collisions = 0");
+        col.capture = on;
+        return PS_OK;
+    }
+
+    int contact_pairs(uint64_t* out, uint64_t cap, uint64_t* count) override {
+        DeviceGuard g(device);
+        if (!cfg.collisions) return fail(PS_ERR_BAD_ARG, "ps_contact_pairs: handle was created with collisions = 0");
+        PS_CUDA_TRY(err, cudaStreamSynchronize(stream));
+        const int rc = check_deferred();
+        if (rc != PS_OK) return rc;
+        return col.read_pairs(out, cap, count, stream, err);
+    }
+
+    int stats(ps_stats* out) override {
+        DeviceGuard g(device);
+        PS_CUDA_TRY(err, cudaStreamSynchronize(stream));
+        std::memset(out, 0, sizeof(*out));
+        out->substeps_done = substeps_done;
+        out->kernel_launches = launches;
+        if (cfg.collisions) {
+            const int rc = col.read_stats(out, stream, err);
+            if (rc != PS_OK) return rc;
+        }
+        return check_deferred();
+    }
+
+    int check_deferred() override {
+        if (!cfg.collisions) return PS_OK;
+        return col.check_flags(stream, err);
+    }
+
+    double dt() const override { return (double)ps::make_step_const<Real>(cfg, false, rows, cols).dt; }
+};
+
+int validate(const ps_config* cfg, uint32_t* rows, uint32_t* cols, std::string* why) {
+    if (!cfg) { *why = "cfg is NULL"; return PS_ERR_BAD_ARG; }
+    if (cfg->struct_size != sizeof(ps_config)) { *why = "cfg->struct_size != sizeof(ps_config) (ABI mismatch)"; return PS_ERR_BAD_ARG; }
+    if (cfg->precision != PS_F64 && cfg->precision != PS_F32) { *why = "unknown precision"; return PS_ERR_BAD_ARG; }
+    if (!(cfg->target_fps > 0) || cfg->sub_steps == 0) { *why = "target_fps and sub_steps must be positive"; return PS_ERR_BAD_ARG; }
+    if (!(cfg->radius > 0) || !(cfg->width > 0) || !(cfg->height > 0)) { *why = "radius, width, height must be positive"; return PS_ERR_BAD_ARG; }
+    if (cfg->count >= (1ull << 28) + 1 && cfg->collisions) { *why = "collision scenes hold at most 2^28 particles per GPU"; return PS_ERR_BAD_ARG; }
+    *rows = *cols = 0;
+    if (cfg->collisions) {
+        // SpatialHashGrid.init: integer division of the truncated values (src/core.zig:61-67)
+        const int32_t wi = (int32_t)cfg->width, hi = (int32_t)cfg->height, gi = (int32_t)cfg->grid_size;
+        if (gi <= 0) { *why = "grid_size truncates to <= 0 (src/core.zig:63)"; return PS_ERR_BAD_ARG; }
+        const int64_t c = wi / gi, r = hi / gi;
+        if (c <= 0 || r <= 0) { *why = "grid has no cells"; return PS_ERR_BAD_ARG; }
+        if (c * r >= (1ll << 31)) { *why = "grid has more than 2^31 cells"; return PS_ERR_BAD_ARG; }
+        *cols = (uint32_t)c; *rows = (uint32_t)r;
+    }
+    return PS_OK;
+}
+
+template <class Real>
+int create_t(const ps_config* cfg, uint32_t rows, uint32_t cols, ps_sim** out) {
+    auto* s = new (std::nothrow) SimT<Real>();
+    if (!s) { g_create_error = "host allocation failed"; return PS_ERR_OOM; }
+    s->cfg = *cfg; s->device = cfg->device; s->n = cfg->count; s->rows = rows; s->cols = cols;
+    const int rc = s->init();
+    if (rc != PS_OK) { g_create_error = s->err.text; delete s; return rc; }
+    *out = s;
+    return PS_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int ps_abi_version(void) { return PS_ABI_VERSION; }
+
+const char* ps_status_string(int status) {
+    switch (status) {
+        case PS_OK: return "ok";
+        case PS_ERR_BAD_ARG: return "bad argument";
+        case PS_ERR_OOM: return "out of memory";
+        case PS_ERR_CUDA: return "CUDA error";
+        case PS_ERR_NCCL: return "NCCL error";
+        case PS_ERR_CELL_OVERFLOW: return "grid cell holds more than 255 particles";
+        case PS_ERR_CAPACITY: return "contact list capacity exceeded";
+        case PS_ERR_NO_DEVICE: return "no CUDA device";
+        default: return "unknown status";
+    }
+}
+
+const char* ps_last_error(const ps_sim* sim) { return sim ? sim->err.text.c_str() : g_create_error.c_str(); }
+
+int ps_create(const ps_config* cfg, ps_sim** out) {
+    if (!out) { g_create_error = "out is NULL"; return PS_ERR_BAD_ARG; }
+    *out = nullptr;
+    uint32_t rows = 0, cols = 0;
+    std::string why;
+    int rc = validate(cfg, &rows, &cols, &why);
+    if (rc != PS_OK) { g_create_error = "ps_create: " + why; return rc; }
+    int ndev = 0;
+    const cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        g_create_error = std::string("ps_create: no CUDA device (") + cudaGetErrorString(e) + "); this library has no CPU path";
+        return PS_ERR_NO_DEVICE;
+    }
+    if (cfg->device < 0 || cfg->device >= ndev) { g_create_error = "ps_create: device ordinal out of range"; return PS_ERR_BAD_ARG; }
+    return cfg->precision == PS_F64 ? create_t<double>(cfg, rows, cols, out) : create_t<float>(cfg, rows, cols, out);
+}
+
+void ps_destroy(ps_sim* sim) { delete sim; }
+
+int ps_upload(ps_sim* s, const double* pos, const double* vel) { return s ? s->upload(pos, vel, true) : PS_ERR_BAD_ARG; }
+int ps_upload_f32(ps_sim* s, const float* pos, const float* vel) { return s ? s->upload(pos, vel, false) : PS_ERR_BAD_ARG; }
+int ps_download(ps_sim* s, double* pos, double* vel) { return s ? s->download(pos, vel, true) : PS_ERR_BAD_ARG; }
+int ps_download_f32(ps_sim* s, float* pos, float* vel) { return s ? s->download(pos, vel, false) : PS_ERR_BAD_ARG; }
+
+int ps_download_acc(ps_sim* s, double* acc_xy) {
+    if (!s || !acc_xy) return PS_ERR_BAD_ARG;
+    // accelerations = (zeroNearZero(0), zeroNearZero(g)) after a gravity step, else (0,0)  src/core.zig:249-257
+    double ay = 0.0;
+    if (s->stepped_with_acc) {
+        ay = s->cfg.precision == PS_F32 ? (double)(float)s->cfg.g : s->cfg.g;
+        if ((ay < 0 ? -ay : ay) < (s->cfg.precision == PS_F32 ? (double)1e-6f : 1e-6)) ay = 0.0;
+    }
+    for (uint64_t i = 0; i < s->n; ++i) { acc_xy[2 * i] = 0.0; acc_xy[2 * i + 1] = ay; }
+    return PS_OK;
+}
+
+int ps_step(ps_sim* s, uint64_t frames) { return s ? s->step(frames * s->cfg.sub_steps) : PS_ERR_BAD_ARG; }
+int ps_step_substeps(ps_sim* s, uint64_t substeps) { return s ? s->step(substeps) : PS_ERR_BAD_ARG; }
+int ps_toggle_acc(ps_sim* s) { if (!s) return PS_ERR_BAD_ARG; s->t_acc = !s->t_acc; return PS_OK; }
+int ps_set_acc(ps_sim* s, int on) { if (!s) return PS_ERR_BAD_ARG; s->t_acc = on != 0; return PS_OK; }
+int ps_get_acc(const ps_sim* s) { return s ? (s->t_acc ? 1 : 0) : PS_ERR_BAD_ARG; }
+
+int ps_sync(ps_sim* s) {
+    if (!s) return PS_ERR_BAD_ARG;
+    DeviceGuard g(s->device);
+    PS_CUDA_TRY(s->err, cudaStreamSynchronize(s->stream));
+    return s->check_deferred();
+}
+
+int ps_set_stream(ps_sim* s, void* cuda_stream) {
+    if (!s) return PS_ERR_BAD_ARG;
+    DeviceGuard g(s->device);
+    PS_CUDA_TRY(s->err, cudaStreamSynchronize(s->stream));
+    s->stream = cuda_stream ? (cudaStream_t)cuda_stream : s->own_stream;
+    return PS_OK;
+}
+
+int ps_grid_shape(const ps_sim* s, uint64_t* rows, uint64_t* cols) {
+    if (!s || !rows || !cols) return PS_ERR_BAD_ARG;
+    if (s->cfg.collisions) { *rows = s->rows; *cols = s->cols; return PS_OK; }
+    const int32_t wi = (int32_t)s->cfg.width, hi = (int32_t)s->cfg.height, gi = (int32_t)s->cfg.grid_size;
+    if (gi <= 0) return PS_ERR_BAD_ARG;
+    *cols = (uint64_t)(wi / gi); *rows = (uint64_t)(hi / gi);
+    return PS_OK;
+}
+
+double ps_dt(const ps_sim* s) { return s ? s->dt() : 0.0; }
+int ps_capture_pairs(ps_sim* s, int on) { return s ? s->capture_pairs(on != 0) : PS_ERR_BAD_ARG; }
+int ps_contact_pairs(ps_sim* s, uint64_t* out, uint64_t cap, uint64_t* count) {
+    if (!s || !count || (cap && !out)) return PS_ERR_BAD_ARG;
+    return s->contact_pairs(out, cap, count);
+}
+int ps_get_stats(ps_sim* s, ps_stats* out) { return (s && out) ? s->stats(out) : PS_ERR_BAD_ARG; }
+int ps_device_state(ps_sim* s, void** px, void** py, void** vx, void** vy) { return s ? s->device_state(px, py, vx, vy) : PS_ERR_BAD_ARG; }
+
+int ps_host_alloc(void** ptr, uint64_t bytes) {
+    if (!ptr) return PS_ERR_BAD_ARG;
+    const cudaError_t e = cudaHostAlloc(ptr, bytes, cudaHostAllocPortable | cudaHostAllocMapped);
+    if (e != cudaSuccess) { cudaGetLastError(); *ptr = nullptr; return e == cudaErrorMemoryAllocation ? PS_ERR_OOM : PS_ERR_NO_DEVICE; }
+    return PS_OK;
+}
+int ps_host_free(void* ptr) { return cudaFreeHost(ptr) == cudaSuccess ? PS_OK : PS_ERR_CUDA; }
+
+// Tuning hook (not part of the stable ABI): pick the integrate kernel variant, 0 = auto.
+int ps_debug_set_integrate_variant(ps_sim* s, int variant) { if (!s) return PS_ERR_BAD_ARG; s->integrate_variant = variant; return PS_OK; }
+int ps_debug_set_transfer_mode(ps_sim* s, int mode) { if (!s) return PS_ERR_BAD_ARG; s->transfer_mode = mode; return PS_OK; }
+
+static int integrate_raw_check(const ps_config* cfg, const void* a, const void* b, const void* c, const void* d, uint64_t count) {
+    if (!cfg || cfg->struct_size != sizeof(ps_config)) return PS_ERR_BAD_ARG;
+    if (count && (!a || !b || !c || !d)) return PS_ERR_BAD_ARG;
+    if (((uintptr_t)a | (uintptr_t)b | (uintptr_t)c | (uintptr_t)d) & 15) return PS_ERR_BAD_ARG;
+    if (!(cfg->target_fps > 0) || cfg->sub_steps == 0) return PS_ERR_BAD_ARG;
+    return PS_OK;
+}
+
+int ps_integrate_bounce_f32(const ps_config* cfg, int t_acc, float* px, float* py, float* vx, float* vy,
+                            uint64_t count, uint64_t substeps, void* cuda_stream) {
+    const int rc = integrate_raw_check(cfg, px, py, vx, vy, count);
+    if (rc != PS_OK) return rc;
+    const ps::StepConst<float> k = ps::make_step_const<float>(*cfg, t_acc != 0, 0, 0);
+    const uint64_t fuse = cfg->fuse_substeps > 1 ? cfg->fuse_substeps : 1;
+    for (uint64_t left = substeps; left;) {
+        const uint64_t now = left < fuse ? left : fuse;
+        if (ps::launch_integrate_bounce<float>(px, py, vx, vy, ps::round_up(count, 4), k, (int)now, 0, (cudaStream_t)cuda_stream) != cudaSuccess) return PS_ERR_CUDA;
+        left -= now;
+    }
+    return PS_OK;
+}
+
+int ps_integrate_bounce_f64(const ps_config* cfg, int t_acc, double* px, double* py, double* vx, double* vy,
+                            uint64_t count, uint64_t substeps, void* cuda_stream) {
+    const int rc = integrate_raw_check(cfg, px, py, vx, vy, count);
+    if (rc != PS_OK) return rc;
+    const ps::StepConst<double> k = ps::make_step_const<double>(*cfg, t_acc != 0, 0, 0);
+    const uint64_t fuse = cfg->fuse_substeps > 1 ? cfg->fuse_substeps : 1;
+    for (uint64_t left = substeps; left;) {
+        const uint64_t now = left < fuse ? left : fuse;
+        if (ps::launch_integrate_bounce<double>(px, py, vx, vy, ps::round_up(count, 4), k, (int)now, 0, (cudaStream_t)cuda_stream) != cudaSuccess) return PS_ERR_CUDA;
+        left -= now;
+    }
+    return PS_OK;
+}
+
+}  // extern "C"
