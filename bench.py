@@ -130,11 +130,11 @@ def run_reference(args):
 
 def workload_config(args, precision):
     return {
-        "workload": f"{args.particles >> 20}Mi particles per GPU, integrate + wall bounce, {precision} SoA "
+        "workload": f"{args.particles >> 20}Mi particles per GPU, integrate + wall bounce "
                     f"(BASELINE.json configs[2]); step = one updatePhysics frame = 8 sub-steps",
         "particles_per_gpu": args.particles, "sub_steps": 8, "scene": "reference constants, world at 0.444 particles/cell",
         "sharding": "particle index range per rank, no collective",
-        "l2": f"state {args.particles * BYTES_PER_UPDATE[precision] // 2 >> 20} MiB per GPU > 126 MB L2, no flush needed",
+        "l2": f"state >= {args.particles * 16 >> 20} MiB per GPU (fp32 SoA), larger than the 126 MB L2: no flush needed",
     }
 
 
