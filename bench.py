@@ -279,7 +279,10 @@ def run_ours(args):
     spawn_chunked(scene_all, 1, rank * n, n, np.float64, hp, hv)
     log(f"[rank {rank}] spawned {n} particles in {time.time() - t0:.1f}s")
 
+    # a real (non-default) stream: the library queues its kernels on it and torch's events time it
+    torch.cuda.set_stream(torch.cuda.Stream())
     stream = torch.cuda.current_stream().cuda_stream
+    assert stream != 0
     sim = Simulation(scene, precision=prec, collisions=False, device=local)
     sim.set_stream(stream)
     sim.debug_set_integrate_variant(args.variant)

@@ -220,7 +220,7 @@ __global__ void __launch_bounds__(256)
 fill_contacts_kernel(const Rec<Real>* __restrict__ rec, const uint32_t* __restrict__ cell_start,
                      const uint32_t* __restrict__ sorted_id, const uint32_t* __restrict__ cell_id, uint32_t n,
                      StepConst<Real> k, const uint32_t* __restrict__ inc_off, uint32_t* __restrict__ entries, uint32_t entries_cap,
-                     unsigned long long* __restrict__ head, uint32_t* __restrict__ wstamp,
+                     unsigned long long* __restrict__ head,
                      const uint32_t* __restrict__ ctr_off, uint64_t* __restrict__ pairs, uint32_t pairs_cap,
                      DevState* __restrict__ ds) {
     const uint32_t a = blockIdx.x * blockDim.x + threadIdx.x;
@@ -233,8 +233,7 @@ fill_contacts_kernel(const Rec<Real>* __restrict__ rec, const uint32_t* __restri
     const uint32_t id_a = sorted_id[a];
     const uint32_t c = cell_id[id_a];
     uint32_t w = inc_off[a];
-    head[a] = (unsigned long long)w;                         // advanced-in-round stamp 0 = never
-    wstamp[a] = 0u;
+    head[a] = (unsigned long long)w;                         // high word: 1 + round of the last advance (0 = none yet)
     const bool cap_pairs = pairs != nullptr && ds->ctr_total <= pairs_cap;
     uint32_t pw = cap_pairs ? ctr_off[a] : 0u;
     walk_contacts<Real>(a, rec, cell_start, c, k, [&](uint32_t q, uint32_t o, uint32_t centre) {
@@ -289,9 +288,8 @@ __device__ __forceinline__ void worklist_push(uint32_t* __restrict__ list, uint3
 template <class Real>
 __global__ void __launch_bounds__(256)
 resolve_kernel(Rec<Real>* __restrict__ rec, const uint32_t* __restrict__ inc_off, const uint32_t* __restrict__ entries,
-               unsigned long long* __restrict__ head, uint32_t* __restrict__ wstamp,
-               uint32_t* __restrict__ wl0, uint32_t* __restrict__ wl1, uint32_t* __restrict__ wl2,
-               uint32_t n, StepConst<Real> k, DevState* __restrict__ ds) {
+               unsigned long long* head, uint32_t* wl0, uint32_t* wl1, uint32_t* wl2,
+               uint32_t n, StepConst<Real> k, DevState* ds) {
     cg::grid_group grid = cg::this_grid();
     const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x;
     const uint32_t nthreads = gridDim.x * blockDim.x;
@@ -303,7 +301,7 @@ resolve_kernel(Rec<Real>* __restrict__ rec, const uint32_t* __restrict__ inc_off
         const uint32_t cnt = r == 0 ? n : __ldcg(&ds->wl_count[cur]);
         if (cnt == 0) break;
         if (tid == 0) ds->wl_count[nn] = 0;                  // consumed in round r-1, refilled in round r+1
-        const uint32_t* __restrict__ wl = lists[cur];
+        const uint32_t* wl = lists[cur];
         for (uint32_t idx = tid; idx < cnt; idx += nthreads) {
             const uint32_t a = r == 0 ? idx : __ldcg(wl + idx);
             const unsigned long long ha = __ldcg(head + a);
@@ -321,7 +319,10 @@ resolve_kernel(Rec<Real>* __restrict__ rec, const uint32_t* __restrict__ inc_off
             const uint32_t eb = entries[ib];
             // same pair seen from the other side: partner = a, same offset, opposite role
             if (eb != (a | (ea & (7u << 28)) | (~ea & (1u << 31)))) continue;
-            if (b < a && __ldcg(wstamp + b) == r) continue;  // both on this round's list: the lower slot runs it
+            // Both particles on this round's list (b's head last moved in round r-1, or never when r = 0): the
+            // lower slot runs the pair.  Membership is read from the SAME 64-bit word as the head index, so a
+            // concurrent executor cannot make the two threads disagree.
+            if (b < a && (uint32_t)(hb >> 32) == r) continue;
             const bool a_centre = (ea >> 31) != 0;
             const uint32_t si = a_centre ? b : a, sj = a_centre ? a : b;   // entry = {particle_i = neighbour, particle_j = centre}
             Rec<Real> I = ld_rec_cg(rec + si), J = ld_rec_cg(rec + sj);
@@ -331,8 +332,8 @@ resolve_kernel(Rec<Real>* __restrict__ rec, const uint32_t* __restrict__ inc_off
             const unsigned long long stamp = (unsigned long long)(r + 1) << 32;
             head[a] = stamp | (ia + 1);
             head[b] = stamp | (ib + 1);
-            if (ia + 1 < end_a) { wstamp[a] = r + 1; worklist_push(lists[nxt], &ds->wl_count[nxt], a); }
-            if (ib + 1 < end_b) { wstamp[b] = r + 1; worklist_push(lists[nxt], &ds->wl_count[nxt], b); }
+            if (ia + 1 < end_a) worklist_push(lists[nxt], &ds->wl_count[nxt], a);
+            if (ib + 1 < end_b) worklist_push(lists[nxt], &ds->wl_count[nxt], b);
         }
         grid.sync();
     }
@@ -359,7 +360,7 @@ struct Collider {
     uint32_t *inc_count = nullptr, *inc_off = nullptr, *ctr_count = nullptr, *ctr_off = nullptr;
     uint32_t* entries = nullptr; uint32_t entries_cap = 0;
     unsigned long long* head = nullptr;
-    uint32_t *wstamp = nullptr, *wl[3] = {nullptr, nullptr, nullptr};
+    uint32_t* wl[3] = {nullptr, nullptr, nullptr};
     uint64_t* pairs = nullptr; uint32_t pairs_cap = 0;
     DevState* ds = nullptr;
 
@@ -389,7 +390,6 @@ struct Collider {
         if ((rc = alloc(&inc_off, n + 1, err))) return rc;
         if ((rc = alloc(&entries, (uint64_t)entries_cap, err))) return rc;
         if ((rc = alloc(&head, n, err))) return rc;
-        if ((rc = alloc(&wstamp, n, err))) return rc;
         for (int i = 0; i < 3; ++i) if ((rc = alloc(&wl[i], n, err))) return rc;
         if ((rc = alloc(&ds, 1, err))) return rc;
         PS_CUDA_TRY(err, cudaMemsetAsync(ds, 0, sizeof(DevState), st));
@@ -406,7 +406,7 @@ struct Collider {
     void destroy() {
         cudaFree(cell_count); cudaFree(cell_start); cudaFree(scan_sums); cudaFree(cell_id); cudaFree(arrival);
         cudaFree(tmp_slot_id); cudaFree(sorted_id); cudaFree(rec); cudaFree(inc_count); cudaFree(inc_off);
-        cudaFree(ctr_count); cudaFree(ctr_off); cudaFree(entries); cudaFree(head); cudaFree(wstamp);
+        cudaFree(ctr_count); cudaFree(ctr_off); cudaFree(entries); cudaFree(head);
         for (auto& w : wl) cudaFree(w);
         cudaFree(pairs); cudaFree(ds);
     }
@@ -439,12 +439,12 @@ struct Collider {
             PS_CUDA_TRY(err, exclusive_scan_u32(ctr_count, ctr_off, n, scan_sums, &ds->ctr_total, nullptr, st));
         }
         fill_contacts_kernel<Real><<<gn, 256, 0, st>>>(rec, cell_start, sorted_id, cell_id, n32, k, inc_off, entries, entries_cap,
-                                                       head, wstamp, capture ? ctr_off : nullptr, capture ? pairs : nullptr, pairs_cap, ds);
+                                                       head, capture ? ctr_off : nullptr, capture ? pairs : nullptr, pairs_cap, ds);
         {
             Rec<Real>* a_rec = rec; const uint32_t* a_off = inc_off; const uint32_t* a_ent = entries;
-            unsigned long long* a_head = head; uint32_t* a_ws = wstamp; uint32_t *a0 = wl[0], *a1 = wl[1], *a2 = wl[2];
+            unsigned long long* a_head = head; uint32_t *a0 = wl[0], *a1 = wl[1], *a2 = wl[2];
             uint32_t a_n = n32; StepConst<Real> a_k = k; DevState* a_ds = ds;
-            void* args[] = {&a_rec, &a_off, &a_ent, &a_head, &a_ws, &a0, &a1, &a2, &a_n, &a_k, &a_ds};
+            void* args[] = {&a_rec, &a_off, &a_ent, &a_head, &a0, &a1, &a2, &a_n, &a_k, &a_ds};
             const uint64_t want = (n + 255) / 256;
             const unsigned grid = (unsigned)(want < (uint64_t)resolve_grid ? want : (uint64_t)resolve_grid);
             PS_CUDA_TRY(err, cudaLaunchCooperativeKernel((const void*)resolve_kernel<Real>, dim3(grid), dim3(256), args, 0, st));
