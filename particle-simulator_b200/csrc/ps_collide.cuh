@@ -485,6 +485,7 @@ struct Collider {
     }
 
     int read_pairs(uint64_t* out, uint64_t cap, uint64_t* count, cudaStream_t st, Error& err) {
+        if (capture && n == 0) { *count = 0; return PS_OK; }   // an empty scene has an empty list
         if (!capture || !pairs) { err.status = PS_ERR_BAD_ARG; err.text = "ps_contact_pairs: call ps_capture_pairs(sim, 1) before stepping"; return err.status; }
         DevState h{};
         PS_CUDA_TRY(err, cudaMemcpyAsync(&h, ds, sizeof(DevState), cudaMemcpyDeviceToHost, st));
