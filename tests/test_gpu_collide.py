@@ -29,8 +29,9 @@ def check(scene, seed, substeps, precision, t_acc, **kw):
     assert np.array_equal(pairs, out["pairs"]), "ordered pair list of the last sub-step differs"
     assert_bit_exact(got_p, want_p, "positions")
     assert_bit_exact(got_v, want_v, "velocities")
-    rel = np.abs(got_p.astype(np.float64) - want_p.astype(np.float64)).max() / np.abs(want_p).max()
-    assert rel <= REL_TOL
+    if scene.count:
+        rel = np.abs(got_p.astype(np.float64) - want_p.astype(np.float64)).max() / np.abs(want_p).max()
+        assert rel <= REL_TOL
     return stats, out
 
 

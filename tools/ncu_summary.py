@@ -1,0 +1,90 @@
+#!/usr/bin/env python
+"""Turn ncu outputs brought back in gpurun_out/ into the small text summaries kept under profiles/.
+
+    python tools/ncu_summary.py launches <launches.csv> <out.md>          # per-kernel totals and shares of a launch list
+    python tools/ncu_summary.py full <report.ncu-rep> <out.csv> [--traffic-json profiles/roofline_traffic.json]
+"""
+import collections
+import csv
+import io
+import json
+import subprocess
+import sys
+
+SCALE = {"ns": 1e-6, "us": 1e-3, "ms": 1.0, "s": 1e3, "nsecond": 1e-6, "usecond": 1e-3, "msecond": 1.0, "second": 1e3}
+KEEP = [
+    "Kernel Name", "launch__grid_size", "launch__block_size", "launch__registers_per_thread",
+    "gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum",
+    "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "dram__cycles_active.avg",
+    "lts__t_bytes.sum", "lts__t_sector_hit_rate.pct", "l1tex__t_sector_hit_rate.pct",
+    "sm__throughput.avg.pct_of_peak_sustained_elapsed", "sm__warps_active.avg.pct_of_peak_sustained_active",
+    "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active", "smsp__cycles_active.avg",
+    "l1tex__t_sectors_pipe_lsu_mem_global_op_ld.sum", "l1tex__t_requests_pipe_lsu_mem_global_op_ld.sum",
+    "l1tex__t_sectors_pipe_lsu_mem_global_op_st.sum", "l1tex__t_requests_pipe_lsu_mem_global_op_st.sum",
+    "smsp__average_warp_latency_issue_stalled_long_scoreboard.ratio", "smsp__warp_issue_stalled_long_scoreboard_per_warp_active.pct",
+    "smsp__warp_issue_stalled_lg_throttle_per_warp_active.pct", "smsp__warp_issue_stalled_barrier_per_warp_active.pct",
+    "smsp__warp_issue_stalled_membar_per_warp_active.pct",
+]
+BYTES = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12}
+
+
+def launches(path, out):
+    with open(path) as fh:
+        lines = [l for l in fh if not l.startswith("==")]
+    agg, cnt = collections.OrderedDict(), collections.Counter()
+    for r in csv.DictReader(io.StringIO("".join(lines))):
+        try:
+            v = float(r["Metric Value"].replace(",", "")) * SCALE[r["Metric Unit"]]
+        except (KeyError, ValueError):
+            continue
+        name = r["Kernel Name"].split("(")[0].replace("void ", "")
+        agg[name] = agg.get(name, 0.0) + v
+        cnt[name] += 1
+    tot = sum(agg.values())
+    with open(out, "w") as f:
+        f.write(f"# ncu launch list summary of `{path}`\n\n")
+        f.write("`ncu --metrics gpu__time_duration.sum --clock-control none` - per-launch times are cold-cache and serialised: compare shares, not absolutes.\n\n")
+        f.write(f"total device time of the captured launches: {tot:.3f} ms over {sum(cnt.values())} launches\n\n")
+        f.write("| kernel | launches | total ms | avg ms | share |\n|---|---:|---:|---:|---:|\n")
+        for k, v in sorted(agg.items(), key=lambda x: -x[1]):
+            f.write(f"| `{k}` | {cnt[k]} | {v:.3f} | {v / cnt[k]:.4f} | {100 * v / tot:.1f}% |\n")
+    print(open(out).read())
+
+
+def full(rep, out, traffic_json=None):
+    raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True, check=True).stdout
+    rows = list(csv.reader(io.StringIO(raw)))
+    hdr, units = rows[0], rows[1]
+    cols = [hdr.index(k) for k in KEEP if k in hdr]
+    with open(out, "w", newline="") as f:
+        w = csv.writer(f)
+        w.writerow([hdr[c] for c in cols])
+        w.writerow([units[c] for c in cols])
+        for r in rows[2:]:
+            w.writerow([r[c] for c in cols])
+    per = collections.defaultdict(list)
+    ir, iw, ik = hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum"), hdr.index("Kernel Name")
+    for r in rows[2:]:
+        b = float(r[ir]) * BYTES[units[ir]] + float(r[iw]) * BYTES[units[iw]]
+        name = r[ik].split("(")[0].replace("void ", "")
+        per[name].append(b)
+    summary = {k: sum(v) / len(v) for k, v in per.items()}
+    print(json.dumps(summary, indent=1))
+    if traffic_json:
+        try:
+            cur = json.load(open(traffic_json))
+        except Exception:
+            cur = {}
+        for k, v in summary.items():
+            base = k.split("<")[0]
+            targ = k.split("<")[1].split(",")[0].rstrip(">") if "<" in k else ""
+            cur[f"{base}<{targ}>" if targ else base] = v
+        json.dump(cur, open(traffic_json, "w"), indent=1)
+
+
+if __name__ == "__main__":
+    if sys.argv[1] == "launches":
+        launches(sys.argv[2], sys.argv[3])
+    else:
+        tj = sys.argv[sys.argv.index("--traffic-json") + 1] if "--traffic-json" in sys.argv else None
+        full(sys.argv[2], sys.argv[3], tj)
