@@ -158,6 +158,14 @@ int ps_integrate_bounce_f32(const ps_config* cfg, int t_acc, float* px, float* p
 int ps_integrate_bounce_f64(const ps_config* cfg, int t_acc, double* px, double* py, double* vx, double* vy,
                             uint64_t count, uint64_t substeps, void* cuda_stream);
 
+/* SpatialHashGrid.computeStartArray (src/core.zig:137-142) on caller-owned device memory:
+ * start_array[i] = grid_array[0] + ... + grid_array[i-1] for i in [0, cells].  start_array holds
+ * cells + 1 words; the extra last word is the particle total, which the reference substitutes for
+ * the last cell's end (:168).  start_array may be the same buffer as grid_array.  The per-tile
+ * partial sums (one word per 4096 cells) live in scratch memory that this call allocates and
+ * frees on `cuda_stream` (cudaMallocAsync / cudaFreeAsync). */
+int ps_compute_start_array(const uint32_t* grid_array, uint32_t* start_array, uint64_t cells, void* cuda_stream);
+
 #ifdef __cplusplus
 }
 #endif

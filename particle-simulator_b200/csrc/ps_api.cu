@@ -411,4 +411,15 @@ int ps_integrate_bounce_f64(const ps_config* cfg, int t_acc, double* px, double*
     return PS_OK;
 }
 
+int ps_compute_start_array(const uint32_t* grid_array, uint32_t* start_array, uint64_t cells, void* cuda_stream) {
+    if (!start_array || (cells && !grid_array)) return PS_ERR_BAD_ARG;
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    uint32_t* sums = nullptr;
+    const cudaError_t e = cudaMallocAsync((void**)&sums, (ps::scan_tiles(cells) + 1) * sizeof(uint32_t), st);
+    if (e != cudaSuccess) { cudaGetLastError(); return e == cudaErrorMemoryAllocation ? PS_ERR_OOM : PS_ERR_CUDA; }
+    const cudaError_t k = ps::exclusive_scan_u32(grid_array, start_array, cells, sums, start_array + cells, nullptr, st);
+    const cudaError_t f = cudaFreeAsync(sums, st);
+    return (k == cudaSuccess && f == cudaSuccess) ? PS_OK : PS_ERR_CUDA;
+}
+
 }  // extern "C"
