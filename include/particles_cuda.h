@@ -166,6 +166,24 @@ int ps_integrate_bounce_f64(const ps_config* cfg, int t_acc, double* px, double*
  * frees on `cuda_stream` (cudaMallocAsync / cudaFreeAsync). */
 int ps_compute_start_array(const uint32_t* grid_array, uint32_t* start_array, uint64_t cells, void* cuda_stream);
 
+/* No counterpart in the reference: ps_compute_start_array for callers that must not allocate.
+ * Some users of this library cannot let a device allocation happen inside the call: a render loop
+ * like main.zig's, paced at 60 frames per second, where an allocation may stall the whole GPU for an
+ * unpredictable time; or a host process that handed all device memory to its own pool up front (a
+ * PyTorch process, an engine with a fixed arena), where a late cudaMalloc can simply fail.  This
+ * variant computes exactly what ps_compute_start_array computes and calls no allocator of any kind:
+ * its partial sums go to a 64 KiB array built into the library image (every GPU that loads the
+ * library holds that array until the process exits).
+ *   - limit: cells <= 67 108 864 (16 384 tiles of 4096 cells); larger sizes return PS_ERR_CAPACITY
+ *     with a message in ps_last_error(NULL) and touch nothing.
+ *   - the first call on each device looks up the array's device address; make that first call with
+ *     the device current and before starting any stream capture.
+ *   - all calls on a device share the one array.  Nothing in it has to be cleared between calls (each
+ *     call overwrites what it later reads), but two calls that overlap on the GPU — different streams,
+ *     or different threads — race on it and both results are undefined.  Calls on one stream are safe.
+ * Inputs and outputs are the caller's, as for ps_compute_start_array; in-place use is allowed. */
+int ps_compute_start_array_static(const uint32_t* grid_array, uint32_t* start_array, uint64_t cells, void* cuda_stream);
+
 #ifdef __cplusplus
 }
 #endif

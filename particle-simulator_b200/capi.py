@@ -98,6 +98,7 @@ SYMBOLS = {
     "ps_integrate_bounce_f32": (ctypes.c_int, [_CFG, ctypes.c_int, _P, _P, _P, _P, _U64, _U64, _P]),
     "ps_integrate_bounce_f64": (ctypes.c_int, [_CFG, ctypes.c_int, _P, _P, _P, _P, _U64, _U64, _P]),
     "ps_compute_start_array": (ctypes.c_int, [_P, _P, _U64, _P]),
+    "ps_compute_start_array_static": (ctypes.c_int, [_P, _P, _U64, _P]),
 }
 
 # not part of the stable ABI (tuning hooks used by bench.py --sweep)

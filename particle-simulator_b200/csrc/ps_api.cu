@@ -7,6 +7,7 @@
 
 #include <cstring>
 #include <memory>
+#include <mutex>
 #include <new>
 #include <string>
 
@@ -420,6 +421,55 @@ int ps_compute_start_array(const uint32_t* grid_array, uint32_t* start_array, ui
     const cudaError_t k = ps::exclusive_scan_u32(grid_array, start_array, cells, sums, start_array + cells, nullptr, st);
     const cudaError_t f = cudaFreeAsync(sums, st);
     return (k == cudaSuccess && f == cudaSuccess) ? PS_OK : PS_ERR_CUDA;
+}
+
+// ---- ps_compute_start_array_static: the same prefix sum with no allocation anywhere ------------------
+//
+// Scratch for the per-tile partial sums lives in the file-scope device array below instead of memory
+// obtained at call time.  64 KiB per GPU that loads this library, held until the process exits.
+// One word per 4096-cell tile => at most PS_STATIC_SCAN_MAX_CELLS cells per call.
+#define PS_STATIC_SCAN_MAX_TILES 16384u
+#define PS_STATIC_SCAN_MAX_CELLS ((uint64_t)PS_STATIC_SCAN_MAX_TILES * (uint64_t)ps::SCAN_TILE)   /* 67 108 864 */
+static __device__ __align__(256) uint32_t g_static_scan_sums[PS_STATIC_SCAN_MAX_TILES];
+
+namespace {
+constexpr int kMaxDevices = 64;
+std::mutex g_static_scan_mutex;
+uint32_t* g_static_scan_ptr[kMaxDevices] = {};   // device address of g_static_scan_sums, per device
+
+// In host code `g_static_scan_sums` is only a handle for the runtime, not an address a kernel can
+// use, and every device has its own copy of the array.  Resolve the real address once per device,
+// with that device current, and remember it.
+int static_scan_scratch(uint32_t** out) {
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDevices) { cudaGetLastError(); return PS_ERR_NO_DEVICE; }
+    std::lock_guard<std::mutex> lock(g_static_scan_mutex);
+    if (!g_static_scan_ptr[dev]) {
+        void* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_static_scan_sums);
+        if (e != cudaSuccess || !p) { cudaGetLastError(); return PS_ERR_CUDA; }
+        g_static_scan_ptr[dev] = static_cast<uint32_t*>(p);
+    }
+    *out = g_static_scan_ptr[dev];
+    return PS_OK;
+}
+}  // namespace
+
+int ps_compute_start_array_static(const uint32_t* grid_array, uint32_t* start_array, uint64_t cells, void* cuda_stream) {
+    if (!start_array || (cells && !grid_array)) return PS_ERR_BAD_ARG;
+    if (cells > PS_STATIC_SCAN_MAX_CELLS) {
+        g_create_error = "ps_compute_start_array_static: " + std::to_string(cells) + " cells exceed the built-in scratch (" +
+                         std::to_string(PS_STATIC_SCAN_MAX_CELLS) + " cells); use ps_compute_start_array";
+        return PS_ERR_CAPACITY;
+    }
+    uint32_t* sums = nullptr;
+    const int rc = static_scan_scratch(&sums);      // first call on this device resolves the symbol address
+    if (rc != PS_OK) return rc;
+    // Every partial sum the scan reads is written earlier in the same call, so nothing left over from
+    // the previous call needs clearing.
+    const cudaError_t k = ps::exclusive_scan_u32(grid_array, start_array, cells, sums, start_array + cells, nullptr,
+                                                 (cudaStream_t)cuda_stream);
+    return k == cudaSuccess ? PS_OK : PS_ERR_CUDA;
 }
 
 }  // extern "C"
