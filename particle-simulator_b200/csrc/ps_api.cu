@@ -127,10 +127,15 @@ struct SimT final : ps_sim {
         DeviceGuard g(device);
         if (n == 0) return PS_OK;
         int rc = PS_OK;
+        if (cfg.collisions) {   // a partial upload (positions only / velocities only) must find the other array current
+            rc = col.materialize_soa(px, py, vx, vy, stream, err, &launches);
+            if (rc != PS_OK) return rc;
+        }
         if (pos) rc = host_f64 ? upload_one((const double*)pos, px, py) : upload_one((const float*)pos, px, py);
         if (rc != PS_OK) return rc;
         if (vel) rc = host_f64 ? upload_one((const double*)vel, vx, vy) : upload_one((const float*)vel, vx, vy);
         if (rc != PS_OK) return rc;
+        if (cfg.collisions && (pos || vel)) col.invalidate_records();
         // the caller may reuse or free its buffers as soon as we return
         PS_CUDA_TRY(err, cudaStreamSynchronize(stream));
         return PS_OK;
@@ -161,6 +166,10 @@ struct SimT final : ps_sim {
         DeviceGuard g(device);
         int rc = PS_OK;
         if (n) {
+            if (cfg.collisions) {   // collision scenes keep the state in cell order; rebuild index order on demand (Q9)
+                rc = col.materialize_soa(px, py, vx, vy, stream, err, &launches);
+                if (rc != PS_OK) return rc;
+            }
             if (pos) rc = host_f64 ? download_one((double*)pos, px, py) : download_one((float*)pos, px, py);
             if (rc != PS_OK) return rc;
             if (vel) rc = host_f64 ? download_one((double*)vel, vx, vy) : download_one((float*)vel, vx, vy);
@@ -195,6 +204,11 @@ struct SimT final : ps_sim {
     }
 
     int device_state(void** ox, void** oy, void** ovx, void** ovy) override {
+        DeviceGuard g(device);
+        if (cfg.collisions && n) {
+            const int rc = col.materialize_soa(px, py, vx, vy, stream, err, &launches);
+            if (rc != PS_OK) return rc;
+        }
         if (ox) *ox = px; if (oy) *oy = py; if (ovx) *ovx = vx; if (ovy) *ovy = vy;
         return PS_OK;
     }

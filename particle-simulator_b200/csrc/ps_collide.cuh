@@ -3,26 +3,34 @@
 //
 // The reference resolves an ordered pair list sequentially (Gauss-Seidel, src/core.zig:211-213);
 // the result depends on that order, so this file reproduces the order instead of
-// approximating it:
+// approximating it.
 //
-//   bin      integrate + bounce (ps_integrate.cuh arithmetic) fused with computeCoordinate /
-//            computeGridIndex (:103-121) and the per-cell count (:124-134, one atomic per particle)
+// State layout.  While a collision scene is being stepped the particles live in `rec`: one
+// 16/32-byte record {px,py,vx,vy} per particle, kept PHYSICALLY IN CELL ORDER ("slots") from one
+// sub-step to the next, with `pid[slot]` = original particle index.  Particles move less than half
+// a cell per sub-step, so the previous order is almost the next one: every pass below reads and
+// writes memory nearly sequentially, and the atomics of the counting sort hit neighbouring
+// counters.  The SoA arrays in original index order are rebuilt only when the caller asks for the
+// state (download / ps_device_state), SURVEY Q9.
+//
+//   bin      integrate + bounce in registers (ps_integrate.cuh arithmetic), computeCoordinate /
+//            computeGridIndex (:103-121), per-cell count (:124-134, one atomic per particle)
 //   scan     computeStartArray (:137-142), ps_scan.cuh
-//   scatter  computeSortedArray (:145-159).  Atomics hand out slots inside a cell in arbitrary
-//            order, so a second kernel ranks each cell's few particles by index, which is the
-//            order the reference's stable counting sort produces; the same kernel gathers
-//            {px,py,vx,vy} into a cell-sorted array of 16/32-byte records ("slots").
-//   detect   every slot walks its 3x3 cell block once in a FIXED segment order that visits its
-//            contacts exactly in the order the reference's pair list (:164-209) mentions that
-//            particle.  The position of an entry in the global list is the lexicographic key
-//            (centre slot, offset index, neighbour slot), so each particle's own sub-list can
-//            be produced without materialising or sorting the global list.
-//   resolve  a pair may run as soon as it heads BOTH of its particles' sub-lists: pairs that
-//            share no particle commute, so executing all such "ready" pairs together, round
-//            after round, is bit-identical to the sequential loop.  One persistent cooperative
-//            kernel runs the rounds (one grid barrier each) over work lists that hold only the
-//            particles whose head changed in the previous round, so total work is O(pairs).
-//   scatter-back  sorted records -> SoA arrays in original index order.
+//   place    particle indices into their cell's slot range, unordered
+//   move     computeSortedArray (:145-159): rank each particle among its cell's indices (ascending
+//            index = what the reference's stable counting sort produces) and write its integrated
+//            record and index to slot cell_start + rank of the other buffer
+//   detect   every slot walks its 3x3 cell block in a FIXED segment order that visits its contacts
+//            exactly in the order the reference's pair list (:164-209) mentions that particle.  The
+//            position of an entry in the global list is the lexicographic key (centre slot, offset
+//            index, neighbour slot), so each particle's own sub-list is produced without
+//            materialising or sorting the global list.  One kernel: count, block scan, one atomic
+//            per CTA for the base, second walk (L1-resident) writes the entries.
+//   resolve  a pair may run as soon as it heads BOTH of its particles' sub-lists: pairs that share
+//            no particle commute, so executing all such "ready" pairs together, round after round,
+//            is bit-identical to the sequential loop.  One persistent cooperative kernel runs the
+//            rounds (one grid barrier each) over work lists that hold only the particles whose head
+//            changed in the previous round, so total work is O(pairs).
 #pragma once
 #include <cooperative_groups.h>
 
@@ -36,9 +44,18 @@ namespace cg = cooperative_groups;
 
 // ---- record types -------------------------------------------------------------------------
 template <class Real> struct Rec;   // one particle: {px, py, vx, vy}
-template <> struct Rec<float>  { float  x, y, u, w; };
-template <> struct Rec<double> { double x, y, u, w; };
+template <> struct __align__(16) Rec<float>  { float  x, y, u, w; };
+template <> struct __align__(16) Rec<double> { double x, y, u, w; };
 
+__device__ __forceinline__ Rec<float> ld_rec(const Rec<float>* p) {
+    const float4 v = *reinterpret_cast<const float4*>(p);
+    return Rec<float>{v.x, v.y, v.z, v.w};
+}
+__device__ __forceinline__ Rec<double> ld_rec(const Rec<double>* p) {
+    const double2 a = reinterpret_cast<const double2*>(p)[0];
+    const double2 b = reinterpret_cast<const double2*>(p)[1];
+    return Rec<double>{a.x, a.y, b.x, b.y};
+}
 __device__ __forceinline__ Rec<float> ld_rec_cg(const Rec<float>* p) {
     const float4 v = __ldcg(reinterpret_cast<const float4*>(p));
     return Rec<float>{v.x, v.y, v.z, v.w};
@@ -69,10 +86,12 @@ __device__ __forceinline__ double floor_r(double x) { return floor(x); }
 struct DevState {
     uint32_t flags;            // bit0: cell overflow (>255), bit1: contact capacity exceeded
     uint32_t max_cell;         // running maximum cell population
-    uint32_t inc_total;        // contact-list entries of this sub-step (= 2 * pairs)
-    uint32_t ctr_total;        // pairs of this sub-step
+    uint32_t entries_used;     // contact-list entries allocated by detect in this sub-step (= 2 * pairs)
+    uint32_t inc_total;        // entries_used of the last completed sub-step
+    uint32_t ctr_total;        // pairs of this sub-step (pair capture only)
     uint32_t wl_count[3];      // rotating work-list lengths
     uint32_t rounds_last;
+    uint32_t pad;
     unsigned long long pairs_total, rounds_total;
 };
 constexpr uint32_t FLAG_CELL_OVERFLOW = 1u, FLAG_CAPACITY = 2u;
@@ -92,62 +111,82 @@ __device__ __forceinline__ uint32_t cell_of(Real x, Real y, const StepConst<Real
     return i * k.rows + j;
 }
 
+// the integrate loop + _applyBoundary on one record (src/core.zig:248-261)
+template <class Real>
+__device__ __forceinline__ void integrate_rec(Rec<Real>& r, const StepConst<Real>& k) {
+    step_component<Real>(r.x, r.u, k.ax_dt, k.dt, k.lo, k.hi_x, k.neg_damp);
+    step_component<Real>(r.y, r.w, k.ay_dt, k.dt, k.lo, k.hi_y, k.neg_damp);
+}
+
+// ---- SoA (original index order) <-> records ---------------------------------------------------
+template <class Real>
+__global__ void __launch_bounds__(256)
+soa_to_rec_kernel(const Real* __restrict__ px, const Real* __restrict__ py, const Real* __restrict__ vx, const Real* __restrict__ vy,
+                  uint32_t n, Rec<Real>* __restrict__ rec, uint32_t* __restrict__ pid) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    st_rec(rec + i, Rec<Real>{px[i], py[i], vx[i], vy[i]});
+    pid[i] = i;
+}
+
+template <class Real>
+__global__ void __launch_bounds__(256)
+rec_to_soa_kernel(const uint32_t* __restrict__ pid, const Rec<Real>* __restrict__ rec, uint32_t n,
+                  Real* __restrict__ px, Real* __restrict__ py, Real* __restrict__ vx, Real* __restrict__ vy) {
+    const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n) return;
+    const uint32_t id = pid[s];
+    const Rec<Real> r = ld_rec(rec + s);
+    px[id] = r.x; py[id] = r.y; vx[id] = r.u; vy[id] = r.w;
+}
+
 // ---- bin: integrate + bounce + cell key + per-cell count ------------------------------------
 template <class Real>
 __global__ void __launch_bounds__(256)
-integrate_bin_kernel(Real* __restrict__ px, Real* __restrict__ py, Real* __restrict__ vx, Real* __restrict__ vy,
-                     uint32_t n, StepConst<Real> k, uint32_t* __restrict__ cell_count,
-                     uint32_t* __restrict__ cell_id, uint32_t* __restrict__ arrival, DevState* __restrict__ ds) {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    if (ds->flags & FLAG_CAPACITY) return;                      // a failed sub-step freezes the state (see ps_status PS_ERR_CAPACITY)
-    Real x = px[i], y = py[i], u = vx[i], w = vy[i];
-    step_component<Real>(x, u, k.ax_dt, k.dt, k.lo, k.hi_x, k.neg_damp);
-    step_component<Real>(y, w, k.ay_dt, k.dt, k.lo, k.hi_y, k.neg_damp);
-    px[i] = x; py[i] = y; vx[i] = u; vy[i] = w;
-    const uint32_t c = cell_of<Real>(x, y, k);
+bin_kernel(const Rec<Real>* __restrict__ rec_old, uint32_t n, StepConst<Real> k, uint32_t* __restrict__ cell_count,
+           uint32_t* __restrict__ slot_cell, uint32_t* __restrict__ arrival, DevState* __restrict__ ds) {
+    const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s == 0) ds->entries_used = 0;                           // detect of this sub-step allocates from zero
+    if (s >= n) return;
+    Rec<Real> r = ld_rec(rec_old + s);
+    integrate_rec<Real>(r, k);
+    const uint32_t c = cell_of<Real>(r.x, r.y, k);
     const uint32_t a = atomicAdd(cell_count + c, 1u);           // grid_array[c] += 1   src/core.zig:132
-    cell_id[i] = c;
-    arrival[i] = a;
+    slot_cell[s] = c;
+    arrival[s] = a;
     if (a >= 255u) atomicOr(&ds->flags, FLAG_CELL_OVERFLOW);    // the reference's u8 would wrap here
 }
 
-// ---- scatter: unordered placement, then rank by particle index inside each cell --------------
+// ---- place + move: the stable counting sort ----------------------------------------------------
 __global__ void __launch_bounds__(256)
-place_kernel(const uint32_t* __restrict__ cell_id, const uint32_t* __restrict__ arrival,
-             const uint32_t* __restrict__ cell_start, uint32_t n, uint32_t* __restrict__ tmp_slot_id) {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    tmp_slot_id[cell_start[cell_id[i]] + arrival[i]] = i;
+place_kernel(const uint32_t* __restrict__ slot_cell, const uint32_t* __restrict__ arrival, const uint32_t* __restrict__ pid_old,
+             const uint32_t* __restrict__ cell_start, uint32_t n, uint32_t* __restrict__ tmp_id) {
+    const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n) return;
+    tmp_id[cell_start[slot_cell[s]] + arrival[s]] = pid_old[s];
 }
 
 template <class Real>
 __global__ void __launch_bounds__(256)
-rank_gather_kernel(const uint32_t* __restrict__ tmp_slot_id, const uint32_t* __restrict__ cell_id,
-                   const uint32_t* __restrict__ cell_start, uint32_t n,
-                   const Real* __restrict__ px, const Real* __restrict__ py, const Real* __restrict__ vx, const Real* __restrict__ vy,
-                   uint32_t* __restrict__ sorted_id, Rec<Real>* __restrict__ rec) {
+move_kernel(const Rec<Real>* __restrict__ rec_old, const uint32_t* __restrict__ pid_old, const uint32_t* __restrict__ slot_cell,
+            const uint32_t* __restrict__ cell_start, const uint32_t* __restrict__ tmp_id, uint32_t n, StepConst<Real> k,
+            Rec<Real>* __restrict__ rec_new, uint32_t* __restrict__ pid_new, const DevState* __restrict__ ds) {
     const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= n) return;
-    const uint32_t id = tmp_slot_id[s];
-    const uint32_t c = cell_id[id];
+    if (ds->flags) {                                         // an earlier sub-step failed: the state stays frozen where it failed
+        st_rec(rec_new + s, ld_rec(rec_old + s));
+        pid_new[s] = pid_old[s];
+        return;
+    }
+    const uint32_t id = pid_old[s];
+    const uint32_t c = slot_cell[s];
     const uint32_t b = cell_start[c], e = cell_start[c + 1];
     uint32_t rank = 0;
-    for (uint32_t t = b; t < e; ++t) rank += tmp_slot_id[t] < id ? 1u : 0u;   // ascending index inside the cell, src/core.zig:146-158
-    const uint32_t dst = b + rank;
-    sorted_id[dst] = id;
-    st_rec(rec + dst, Rec<Real>{px[id], py[id], vx[id], vy[id]});
-}
-
-template <class Real>
-__global__ void __launch_bounds__(256)
-scatter_back_kernel(const uint32_t* __restrict__ sorted_id, const Rec<Real>* __restrict__ rec, uint32_t n,
-                    Real* __restrict__ px, Real* __restrict__ py, Real* __restrict__ vx, Real* __restrict__ vy) {
-    const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
-    if (s >= n) return;
-    const uint32_t id = sorted_id[s];
-    const Rec<Real> r = ld_rec_cg(rec + s);
-    px[id] = r.x; py[id] = r.y; vx[id] = r.u; vy[id] = r.w;
+    for (uint32_t t = b; t < e; ++t) rank += tmp_id[t] < id ? 1u : 0u;   // ascending index inside the cell, src/core.zig:146-158
+    Rec<Real> r = ld_rec(rec_old + s);
+    integrate_rec<Real>(r, k);                                            // same arithmetic as bin_kernel, bit for bit
+    st_rec(rec_new + b + rank, r);
+    pid_new[b + rank] = id;
 }
 
 // ---- detect ----------------------------------------------------------------------------------
@@ -159,13 +198,40 @@ scatter_back_kernel(const uint32_t* __restrict__ sorted_id, const Rec<Real>* __r
 //   2. a as CENTRE: o=0 own cell (q != a), o=1 (gx,gy+1), o=2 (gx+1,gy), o=3 (gx+1,gy+1), o=4 (gx-1,gy+1)
 //   3. a as NEIGHBOUR of later centres: own cell q>a via o=0, cell (gx+1,gy-1) via o=4
 // f(q, o, centre_flag) is called for every overlapping partner slot q (checkCollision, :339-346).
-template <class Real, class F>
-__device__ __forceinline__ void walk_contacts(uint32_t a, const Rec<Real>* __restrict__ rec, const uint32_t* __restrict__ cell_start,
-                                              uint32_t c, const StepConst<Real>& k, F&& f) {
+struct Stencil {   // slot ranges of the 3x3 block around one cell, loaded once and reused by both walks
+    uint32_t l0, l1, l2, l3;   // column gx-1: starts of rows gy-1, gy, gy+1, gy+2
+    uint32_t m0, m1, m2, m3;   // column gx
+    uint32_t r0, r1, r2, r3;   // column gx+1
+    bool up, down, left, right;
+};
+
+template <class Real>
+__device__ __forceinline__ Stencil load_stencil(const uint32_t* __restrict__ cell_start, uint32_t c, const StepConst<Real>& k) {
+    Stencil s{};
     const uint32_t rows = k.rows, cols = k.cols;
     const uint32_t gx = c / rows, gy = c - gx * rows;
+    s.up = gy > 0; s.down = gy + 1 < rows; s.left = gx > 0; s.right = gx + 1 < cols;
+    s.m1 = cell_start[c]; s.m2 = cell_start[c + 1];
+    s.m0 = s.up ? cell_start[c - 1] : s.m1;
+    s.m3 = s.down ? cell_start[c + 2] : s.m2;
+    if (s.left) {
+        const uint32_t cl = c - rows;
+        s.l1 = cell_start[cl]; s.l2 = cell_start[cl + 1];
+        s.l0 = s.up ? cell_start[cl - 1] : s.l1;
+        s.l3 = s.down ? cell_start[cl + 2] : s.l2;
+    }
+    if (s.right) {
+        const uint32_t cr = c + rows;
+        s.r1 = cell_start[cr]; s.r2 = cell_start[cr + 1];
+        s.r0 = s.up ? cell_start[cr - 1] : s.r1;
+        s.r3 = s.down ? cell_start[cr + 2] : s.r2;
+    }
+    return s;
+}
+
+template <class Real, class F>
+__device__ __forceinline__ void walk_contacts(uint32_t a, const Rec<Real>* __restrict__ rec, const Stencil& s, Real r2sq, F&& f) {
     const auto pa = ld_pos(rec + a);
-    const Real r2sq = k.r2sq;
     auto seg = [&](uint32_t b, uint32_t e, uint32_t o, uint32_t centre) {
         for (uint32_t q = b; q < e; ++q) {
             const auto pq = ld_pos(rec + q);
@@ -176,73 +242,96 @@ __device__ __forceinline__ void walk_contacts(uint32_t a, const Rec<Real>* __res
             if (d2 < r2sq) f(q, o, centre);
         }
     };
-    const bool up = gy > 0, down = gy + 1 < rows, left = gx > 0, right = gx + 1 < cols;
-    const uint32_t own_b = cell_start[c], own_e = cell_start[c + 1];
-    // 1. neighbour of earlier centres
-    if (left) {
-        const uint32_t cl = c - rows;
-        if (up) seg(cell_start[cl - 1], cell_start[cl], 3u, 0u);
-        seg(cell_start[cl], cell_start[cl + 1], 2u, 0u);
-    }
-    if (up) seg(cell_start[c - 1], own_b, 1u, 0u);
-    seg(own_b, a, 0u, 0u);
+    // 1. neighbour of earlier centres (empty ranges when the cell does not exist)
+    if (s.left) { seg(s.l0, s.l1, 3u, 0u); seg(s.l1, s.l2, 2u, 0u); }
+    seg(s.m0, s.m1, 1u, 0u);
+    seg(s.m1, a, 0u, 0u);
     // 2. centre
-    seg(own_b, a, 0u, 1u);
-    seg(a + 1, own_e, 0u, 1u);
-    if (down) seg(own_e, cell_start[c + 2], 1u, 1u);
-    if (right) {
-        const uint32_t cr = c + rows;
-        seg(cell_start[cr], cell_start[cr + 1], 2u, 1u);
-        if (down) seg(cell_start[cr + 1], cell_start[cr + 2], 3u, 1u);
-    }
-    if (left && down) { const uint32_t cl = c - rows; seg(cell_start[cl + 1], cell_start[cl + 2], 4u, 1u); }
+    seg(s.m1, a, 0u, 1u);
+    seg(a + 1, s.m2, 0u, 1u);
+    seg(s.m2, s.m3, 1u, 1u);
+    if (s.right) { seg(s.r1, s.r2, 2u, 1u); seg(s.r2, s.r3, 3u, 1u); }
+    if (s.left) seg(s.l2, s.l3, 4u, 1u);
     // 3. neighbour of later centres
-    seg(a + 1, own_e, 0u, 0u);
-    if (right && up) { const uint32_t cr = c + rows; seg(cell_start[cr - 1], cell_start[cr], 4u, 0u); }
+    seg(a + 1, s.m2, 0u, 0u);
+    if (s.right) seg(s.r0, s.r1, 4u, 0u);
 }
 
+// One kernel builds every particle's contact sub-list: count, CTA-wide scan, one atomic per CTA
+// reserves the CTA's range of `entries`, second walk fills it.  Also seeds the first work list.
 template <class Real>
 __global__ void __launch_bounds__(256)
-count_contacts_kernel(const Rec<Real>* __restrict__ rec, const uint32_t* __restrict__ cell_start,
-                      const uint32_t* __restrict__ sorted_id, const uint32_t* __restrict__ cell_id, uint32_t n,
-                      StepConst<Real> k, uint32_t* __restrict__ inc_count, uint32_t* __restrict__ ctr_count) {
+detect_kernel(const Rec<Real>* __restrict__ rec, const uint32_t* __restrict__ cell_start, uint32_t n, StepConst<Real> k,
+              uint32_t* __restrict__ entries, uint32_t entries_cap, unsigned long long* __restrict__ head,
+              uint32_t* __restrict__ list_end, uint32_t* __restrict__ wl0, DevState* __restrict__ ds) {
+    __shared__ uint32_t sh_base, sh_wbase;
     const uint32_t a = blockIdx.x * blockDim.x + threadIdx.x;
-    if (a >= n) return;
-    const uint32_t c = cell_id[sorted_id[a]];
-    uint32_t ninc = 0, nctr = 0;
-    walk_contacts<Real>(a, rec, cell_start, c, k, [&](uint32_t, uint32_t, uint32_t centre) { ++ninc; nctr += centre; });
-    inc_count[a] = ninc;
-    if (ctr_count) ctr_count[a] = nctr;
-}
-
-template <class Real>
-__global__ void __launch_bounds__(256)
-fill_contacts_kernel(const Rec<Real>* __restrict__ rec, const uint32_t* __restrict__ cell_start,
-                     const uint32_t* __restrict__ sorted_id, const uint32_t* __restrict__ cell_id, uint32_t n,
-                     StepConst<Real> k, const uint32_t* __restrict__ inc_off, uint32_t* __restrict__ entries, uint32_t entries_cap,
-                     unsigned long long* __restrict__ head,
-                     const uint32_t* __restrict__ ctr_off, uint64_t* __restrict__ pairs, uint32_t pairs_cap,
-                     DevState* __restrict__ ds) {
-    const uint32_t a = blockIdx.x * blockDim.x + threadIdx.x;
-    if (a >= n) return;
-    if (ds->inc_total > entries_cap) {                       // list does not fit: flag, leave the sub-step at its post-bounce state
-        if (a == 0) atomicOr(&ds->flags, FLAG_CAPACITY);
-        head[a] = (unsigned long long)inc_off[a + 1];        // empty list
+    const bool valid = a < n;
+    if (ds->flags) {                                         // error state (uniform: set by an earlier launch): no lists, no resolve
+        if (valid) { head[a] = 0ull; list_end[a] = 0u; }
         return;
     }
-    const uint32_t id_a = sorted_id[a];
-    const uint32_t c = cell_id[id_a];
-    uint32_t w = inc_off[a];
-    head[a] = (unsigned long long)w;                         // high word: 1 + round of the last advance (0 = none yet)
-    const bool cap_pairs = pairs != nullptr && ds->ctr_total <= pairs_cap;
-    uint32_t pw = cap_pairs ? ctr_off[a] : 0u;
-    walk_contacts<Real>(a, rec, cell_start, c, k, [&](uint32_t q, uint32_t o, uint32_t centre) {
-        entries[w++] = make_entry(q, o, centre);
-        if (cap_pairs && centre) {                           // collision_pairs.append({particle_i, particle_j})  src/core.zig:203
-            pairs[2 * (uint64_t)pw] = sorted_id[q];
-            pairs[2 * (uint64_t)pw + 1] = id_a;
-            ++pw;
-        }
+    Stencil st{};
+    uint32_t cnt = 0;
+    if (valid) {
+        const auto pa = ld_pos(rec + a);
+        st = load_stencil<Real>(cell_start, cell_of<Real>(pa.x, pa.y, k), k);
+        walk_contacts<Real>(a, rec, st, k.r2sq, [&](uint32_t, uint32_t, uint32_t) { ++cnt; });
+    }
+    // packed CTA scan: entry count in the low 22 bits, "has a list" flag above
+    const uint32_t packed = cnt | ((cnt ? 1u : 0u) << 22);
+    uint32_t total;
+    const uint32_t ex = block_exclusive_scan<256>(packed, &total);
+    if (threadIdx.x == 0) {
+        const uint32_t te = total & ((1u << 22) - 1), tw = total >> 22;
+        sh_base = te ? atomicAdd(&ds->entries_used, te) : 0u;
+        sh_wbase = tw ? atomicAdd(&ds->wl_count[0], tw) : 0u;
+    }
+    __syncthreads();
+    if (!valid) return;
+    const uint32_t te = total & ((1u << 22) - 1);
+    const uint32_t begin = sh_base + (ex & ((1u << 22) - 1));
+    if ((uint64_t)sh_base + te > entries_cap) {                  // does not fit: flag; the resolve kernel will not run
+        if (threadIdx.x == 0) atomicOr(&ds->flags, FLAG_CAPACITY);
+        head[a] = 0ull; list_end[a] = 0u;
+        return;
+    }
+    head[a] = (unsigned long long)begin;                         // high word: 1 + round of the last advance (0 = none yet)
+    list_end[a] = begin + cnt;
+    if (cnt) {
+        wl0[sh_wbase + (ex >> 22)] = a;
+        uint32_t w = begin;
+        walk_contacts<Real>(a, rec, st, k.r2sq, [&](uint32_t q, uint32_t o, uint32_t centre) { entries[w++] = make_entry(q, o, centre); });
+    }
+}
+
+// Pair capture (ps_capture_pairs): the global ordered list {particle_i, particle_j} (src/core.zig:203).
+template <class Real>
+__global__ void __launch_bounds__(256)
+count_centre_kernel(const Rec<Real>* __restrict__ rec, const uint32_t* __restrict__ cell_start, uint32_t n, StepConst<Real> k,
+                    uint32_t* __restrict__ ctr_count) {
+    const uint32_t a = blockIdx.x * blockDim.x + threadIdx.x;
+    if (a >= n) return;
+    const auto pa = ld_pos(rec + a);
+    const Stencil st = load_stencil<Real>(cell_start, cell_of<Real>(pa.x, pa.y, k), k);
+    uint32_t c = 0;
+    walk_contacts<Real>(a, rec, st, k.r2sq, [&](uint32_t, uint32_t, uint32_t centre) { c += centre; });
+    ctr_count[a] = c;
+}
+
+template <class Real>
+__global__ void __launch_bounds__(256)
+fill_pairs_kernel(const Rec<Real>* __restrict__ rec, const uint32_t* __restrict__ cell_start, const uint32_t* __restrict__ pid,
+                  uint32_t n, StepConst<Real> k, const uint32_t* __restrict__ ctr_off, uint64_t* __restrict__ pairs,
+                  uint32_t pairs_cap, const DevState* __restrict__ ds) {
+    const uint32_t a = blockIdx.x * blockDim.x + threadIdx.x;
+    if (a >= n || ds->ctr_total > pairs_cap) return;
+    const auto pa = ld_pos(rec + a);
+    const Stencil st = load_stencil<Real>(cell_start, cell_of<Real>(pa.x, pa.y, k), k);
+    uint64_t w = ctr_off[a];
+    const uint64_t id_a = pid[a];
+    walk_contacts<Real>(a, rec, st, k.r2sq, [&](uint32_t q, uint32_t, uint32_t centre) {
+        if (centre) { pairs[2 * w] = pid[q]; pairs[2 * w + 1] = id_a; ++w; }   // {neighbour, centre}
     });
 }
 
@@ -274,73 +363,83 @@ __device__ __forceinline__ void resolve_pair(Rec<Real>& I, Rec<Real>& J, const S
     J.u = J.u + nx * kk; J.w = J.w + ny * kk;                                 // :391
 }
 
-__device__ __forceinline__ void worklist_push(uint32_t* __restrict__ list, uint32_t* __restrict__ count, uint32_t v) {
-    // warp-aggregated append
-    const unsigned m = __activemask();
-    const unsigned lane = threadIdx.x & 31;
-    const int leader = __ffs(m) - 1;
-    uint32_t base = 0;
-    if ((int)lane == leader) base = atomicAdd(count, (uint32_t)__popc(m));
-    base = __shfl_sync(m, base, leader);
-    list[base + __popc(m & ((1u << lane) - 1))] = v;
-}
+constexpr int RESOLVE_THREADS = 256;
 
 template <class Real>
-__global__ void __launch_bounds__(256)
-resolve_kernel(Rec<Real>* __restrict__ rec, const uint32_t* __restrict__ inc_off, const uint32_t* __restrict__ entries,
-               unsigned long long* head, uint32_t* wl0, uint32_t* wl1, uint32_t* wl2,
-               uint32_t n, StepConst<Real> k, DevState* ds) {
+__global__ void __launch_bounds__(RESOLVE_THREADS)
+resolve_kernel(Rec<Real>* rec, const uint32_t* __restrict__ list_end, const uint32_t* __restrict__ entries,
+               unsigned long long* head, uint32_t* wl0, uint32_t* wl1, uint32_t* wl2, StepConst<Real> k, DevState* ds) {
     cg::grid_group grid = cg::this_grid();
-    const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x;
-    const uint32_t nthreads = gridDim.x * blockDim.x;
+    __shared__ uint32_t sh_buf[2 * RESOLVE_THREADS];
+    __shared__ uint32_t sh_cnt, sh_base;
     uint32_t* lists[3] = {wl0, wl1, wl2};
-    if (ds->flags & FLAG_CAPACITY) return;                   // uniform across the grid: set before this launch
+    const bool leader = blockIdx.x == 0 && threadIdx.x == 0;
+    if (ds->flags) {                                         // uniform across the grid: set before this launch
+        if (leader) ds->wl_count[0] = 0;
+        return;
+    }
     uint32_t r = 0;
     for (;; ++r) {
         const uint32_t cur = r % 3, nxt = (r + 1) % 3, nn = (r + 2) % 3;
-        const uint32_t cnt = r == 0 ? n : __ldcg(&ds->wl_count[cur]);
+        const uint32_t cnt = __ldcg(&ds->wl_count[cur]);
         if (cnt == 0) break;
-        if (tid == 0) ds->wl_count[nn] = 0;                  // consumed in round r-1, refilled in round r+1
+        if (leader) ds->wl_count[nn] = 0;                    // consumed in round r-1, refilled in round r+1
         const uint32_t* wl = lists[cur];
-        for (uint32_t idx = tid; idx < cnt; idx += nthreads) {
-            const uint32_t a = r == 0 ? idx : __ldcg(wl + idx);
-            const unsigned long long ha = __ldcg(head + a);
-            if ((uint32_t)(ha >> 32) == r + 1) continue;     // a already ran a pair this round (executed by its partner)
-            const uint32_t ia = (uint32_t)ha;
-            const uint32_t end_a = inc_off[a + 1];
-            if (ia >= end_a) continue;                       // a's list is finished
-            const uint32_t ea = entries[ia];
-            const uint32_t b = ea & ENT_SLOT_MASK;
-            const unsigned long long hb = __ldcg(head + b);
-            if ((uint32_t)(hb >> 32) == r + 1) continue;     // b moved this round; b is on the next list and will look at a
-            const uint32_t ib = (uint32_t)hb;
-            const uint32_t end_b = inc_off[b + 1];
-            if (ib >= end_b) continue;
-            const uint32_t eb = entries[ib];
-            // same pair seen from the other side: partner = a, same offset, opposite role
-            if (eb != (a | (ea & (7u << 28)) | (~ea & (1u << 31)))) continue;
-            // Both particles on this round's list (b's head last moved in round r-1, or never when r = 0): the
-            // lower slot runs the pair.  Membership is read from the SAME 64-bit word as the head index, so a
-            // concurrent executor cannot make the two threads disagree.
-            if (b < a && (uint32_t)(hb >> 32) == r) continue;
-            const bool a_centre = (ea >> 31) != 0;
-            const uint32_t si = a_centre ? b : a, sj = a_centre ? a : b;   // entry = {particle_i = neighbour, particle_j = centre}
-            Rec<Real> I = ld_rec_cg(rec + si), J = ld_rec_cg(rec + sj);
-            resolve_pair<Real>(I, J, k);
-            st_rec(rec + si, I);
-            st_rec(rec + sj, J);
-            const unsigned long long stamp = (unsigned long long)(r + 1) << 32;
-            head[a] = stamp | (ia + 1);
-            head[b] = stamp | (ib + 1);
-            if (ia + 1 < end_a) worklist_push(lists[nxt], &ds->wl_count[nxt], a);
-            if (ib + 1 < end_b) worklist_push(lists[nxt], &ds->wl_count[nxt], b);
+        uint32_t* out = lists[nxt];
+        for (uint32_t base = blockIdx.x * RESOLVE_THREADS; base < cnt; base += gridDim.x * RESOLVE_THREADS) {
+            if (threadIdx.x == 0) sh_cnt = 0;
+            __syncthreads();
+            const uint32_t idx = base + threadIdx.x;
+            do {
+                if (idx >= cnt) break;
+                const uint32_t a = __ldcg(wl + idx);
+                const unsigned long long ha = __ldcg(head + a);
+                if ((uint32_t)(ha >> 32) == r + 1) break;        // a already ran a pair this round (executed by its partner)
+                const uint32_t ia = (uint32_t)ha;
+                const uint32_t end_a = list_end[a];
+                if (ia >= end_a) break;                          // a's list is finished
+                const uint32_t ea = entries[ia];
+                const uint32_t b = ea & ENT_SLOT_MASK;
+                const unsigned long long hb = __ldcg(head + b);
+                if ((uint32_t)(hb >> 32) == r + 1) break;        // b moved this round; b is on the next list and will look at a
+                const uint32_t ib = (uint32_t)hb;
+                const uint32_t end_b = list_end[b];
+                if (ib >= end_b) break;
+                const uint32_t eb = entries[ib];
+                // same pair seen from the other side: partner = a, same offset, opposite role
+                if (eb != (a | (ea & (7u << 28)) | (~ea & (1u << 31)))) break;
+                // Both particles on this round's list (b's head last moved in round r-1, or never when r = 0): the
+                // lower slot runs the pair.  Membership is read from the SAME 64-bit word as the head index, so a
+                // concurrent executor cannot make the two threads disagree.
+                if (b < a && (uint32_t)(hb >> 32) == r) break;
+                const bool a_centre = (ea >> 31) != 0;
+                const uint32_t si = a_centre ? b : a, sj = a_centre ? a : b;   // entry = {particle_i = neighbour, particle_j = centre}
+                Rec<Real> I = ld_rec_cg(rec + si), J = ld_rec_cg(rec + sj);
+                resolve_pair<Real>(I, J, k);
+                st_rec(rec + si, I);
+                st_rec(rec + sj, J);
+                const unsigned long long stamp = (unsigned long long)(r + 1) << 32;
+                head[a] = stamp | (ia + 1);
+                head[b] = stamp | (ib + 1);
+                if (ia + 1 < end_a) sh_buf[atomicAdd(&sh_cnt, 1u)] = a;
+                if (ib + 1 < end_b) sh_buf[atomicAdd(&sh_cnt, 1u)] = b;
+            } while (false);
+            __syncthreads();
+            const uint32_t m = sh_cnt;
+            if (m) {                                             // one global atomic per CTA per batch
+                if (threadIdx.x == 0) sh_base = atomicAdd(&ds->wl_count[nxt], m);
+                __syncthreads();
+                for (uint32_t i = threadIdx.x; i < m; i += RESOLVE_THREADS) out[sh_base + i] = sh_buf[i];
+            }
+            __syncthreads();
         }
         grid.sync();
     }
-    if (tid == 0) {
+    if (leader) {
         ds->rounds_last = r;
         ds->rounds_total += r;
-        ds->pairs_total += ds->inc_total / 2;
+        ds->inc_total = ds->entries_used;
+        ds->pairs_total += ds->entries_used / 2;
         ds->wl_count[0] = ds->wl_count[1] = ds->wl_count[2] = 0;
     }
 }
@@ -351,13 +450,17 @@ struct Collider {
     uint64_t n = 0;
     uint32_t rows = 0, cols = 0, ncell = 0;
     bool capture = false;
+    bool rec_valid = false;    // rec[cur]/pid[cur] hold the current state
+    bool soa_valid = true;     // the caller's SoA arrays hold the current state
+    int cur = 0;
     int device = 0;
     int resolve_grid = 0;
 
     uint32_t *cell_count = nullptr, *cell_start = nullptr, *scan_sums = nullptr;
-    uint32_t *cell_id = nullptr, *arrival = nullptr, *tmp_slot_id = nullptr, *sorted_id = nullptr;
-    Rec<Real>* rec = nullptr;
-    uint32_t *inc_count = nullptr, *inc_off = nullptr, *ctr_count = nullptr, *ctr_off = nullptr;
+    uint32_t *slot_cell = nullptr, *arrival = nullptr, *tmp_id = nullptr;
+    Rec<Real>* rec[2] = {nullptr, nullptr};
+    uint32_t* pid[2] = {nullptr, nullptr};
+    uint32_t *list_end = nullptr, *ctr_count = nullptr, *ctr_off = nullptr;
     uint32_t* entries = nullptr; uint32_t entries_cap = 0;
     unsigned long long* head = nullptr;
     uint32_t* wl[3] = {nullptr, nullptr, nullptr};
@@ -381,20 +484,21 @@ struct Collider {
         if ((rc = alloc(&cell_count, (uint64_t)ncell, err))) return rc;
         if ((rc = alloc(&cell_start, (uint64_t)ncell + 3, err))) return rc;
         if ((rc = alloc(&scan_sums, scan_tiles(scan_len) + 1, err))) return rc;
-        if ((rc = alloc(&cell_id, n, err))) return rc;
+        if ((rc = alloc(&slot_cell, n, err))) return rc;
         if ((rc = alloc(&arrival, n, err))) return rc;
-        if ((rc = alloc(&tmp_slot_id, n, err))) return rc;
-        if ((rc = alloc(&sorted_id, n, err))) return rc;
-        if ((rc = alloc(&rec, n, err))) return rc;
-        if ((rc = alloc(&inc_count, n, err))) return rc;
-        if ((rc = alloc(&inc_off, n + 1, err))) return rc;
+        if ((rc = alloc(&tmp_id, n, err))) return rc;
+        for (int i = 0; i < 2; ++i) {
+            if ((rc = alloc(&rec[i], n, err))) return rc;
+            if ((rc = alloc(&pid[i], n, err))) return rc;
+        }
+        if ((rc = alloc(&list_end, n, err))) return rc;
         if ((rc = alloc(&entries, (uint64_t)entries_cap, err))) return rc;
         if ((rc = alloc(&head, n, err))) return rc;
         for (int i = 0; i < 3; ++i) if ((rc = alloc(&wl[i], n, err))) return rc;
         if ((rc = alloc(&ds, 1, err))) return rc;
         PS_CUDA_TRY(err, cudaMemsetAsync(ds, 0, sizeof(DevState), st));
         int per_sm = 0, sms = 0;
-        PS_CUDA_TRY(err, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, resolve_kernel<Real>, 256, 0));
+        PS_CUDA_TRY(err, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, resolve_kernel<Real>, RESOLVE_THREADS, 0));
         PS_CUDA_TRY(err, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
         int coop = 0;
         PS_CUDA_TRY(err, cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, device));
@@ -404,9 +508,10 @@ struct Collider {
     }
 
     void destroy() {
-        cudaFree(cell_count); cudaFree(cell_start); cudaFree(scan_sums); cudaFree(cell_id); cudaFree(arrival);
-        cudaFree(tmp_slot_id); cudaFree(sorted_id); cudaFree(rec); cudaFree(inc_count); cudaFree(inc_off);
-        cudaFree(ctr_count); cudaFree(ctr_off); cudaFree(entries); cudaFree(head);
+        cudaFree(cell_count); cudaFree(cell_start); cudaFree(scan_sums); cudaFree(slot_cell); cudaFree(arrival);
+        cudaFree(tmp_id); cudaFree(list_end); cudaFree(ctr_count); cudaFree(ctr_off); cudaFree(entries); cudaFree(head);
+        for (auto& r : rec) cudaFree(r);
+        for (auto& p : pid) cudaFree(p);
         for (auto& w : wl) cudaFree(w);
         cudaFree(pairs); cudaFree(ds);
     }
@@ -420,38 +525,60 @@ struct Collider {
         return PS_OK;
     }
 
+    unsigned grid_n() const { return (unsigned)((n + 255) / 256); }
+
+    // The caller wrote new SoA arrays (upload): the records are stale.
+    void invalidate_records() { rec_valid = false; soa_valid = true; }
+
+    // Bring the SoA arrays (original index order) up to date with the records.
+    int materialize_soa(Real* px, Real* py, Real* vx, Real* vy, cudaStream_t st, Error& err, uint64_t* launches) {
+        if (soa_valid || !rec_valid || n == 0) { soa_valid = true; return PS_OK; }
+        rec_to_soa_kernel<Real><<<grid_n(), 256, 0, st>>>(pid[cur], rec[cur], (uint32_t)n, px, py, vx, vy);
+        PS_CUDA_TRY(err, cudaGetLastError());
+        ++*launches;
+        soa_valid = true;
+        return PS_OK;
+    }
+
     // One iteration of the loop body at src/core.zig:247-267.
     int substep(Real* px, Real* py, Real* vx, Real* vy, const StepConst<Real>& k, cudaStream_t st, Error& err, uint64_t* launches) {
         if (n == 0) return PS_OK;
         if (capture) { const int rc = ensure_capture(err); if (rc) return rc; }
         const uint32_t n32 = (uint32_t)n;
-        const unsigned gn = (unsigned)((n + 255) / 256);
+        const unsigned gn = grid_n();
+        if (!rec_valid) {                                    // first sub-step after an upload: records in index order
+            soa_to_rec_kernel<Real><<<gn, 256, 0, st>>>(px, py, vx, vy, n32, rec[cur], pid[cur]);
+            rec_valid = true;
+            ++*launches;
+        }
+        soa_valid = false;
+        const int nw = cur ^ 1;
         // shg.clear() (:262) — only the counters need it; every other array is fully rewritten
         PS_CUDA_TRY(err, cudaMemsetAsync(cell_count, 0, (uint64_t)ncell * sizeof(uint32_t), st));
-        integrate_bin_kernel<Real><<<gn, 256, 0, st>>>(px, py, vx, vy, n32, k, cell_count, cell_id, arrival, ds);
+        bin_kernel<Real><<<gn, 256, 0, st>>>(rec[cur], n32, k, cell_count, slot_cell, arrival, ds);
         PS_CUDA_TRY(err, exclusive_scan_u32(cell_count, cell_start, ncell, scan_sums, cell_start + ncell, &ds->max_cell, st));
-        place_kernel<<<gn, 256, 0, st>>>(cell_id, arrival, cell_start, n32, tmp_slot_id);
-        rank_gather_kernel<Real><<<gn, 256, 0, st>>>(tmp_slot_id, cell_id, cell_start, n32, px, py, vx, vy, sorted_id, rec);
-        count_contacts_kernel<Real><<<gn, 256, 0, st>>>(rec, cell_start, sorted_id, cell_id, n32, k, inc_count, capture ? ctr_count : nullptr);
-        PS_CUDA_TRY(err, exclusive_scan_u32(inc_count, inc_off, n, scan_sums, &ds->inc_total, nullptr, st));
-        PS_CUDA_TRY(err, cudaMemcpyAsync(inc_off + n, &ds->inc_total, sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
+        place_kernel<<<gn, 256, 0, st>>>(slot_cell, arrival, pid[cur], cell_start, n32, tmp_id);
+        move_kernel<Real><<<gn, 256, 0, st>>>(rec[cur], pid[cur], slot_cell, cell_start, tmp_id, n32, k, rec[nw], pid[nw], ds);
+        detect_kernel<Real><<<gn, 256, 0, st>>>(rec[nw], cell_start, n32, k, entries, entries_cap, head, list_end, wl[0], ds);
+        *launches += 7;
         if (capture) {
+            count_centre_kernel<Real><<<gn, 256, 0, st>>>(rec[nw], cell_start, n32, k, ctr_count);
             PS_CUDA_TRY(err, exclusive_scan_u32(ctr_count, ctr_off, n, scan_sums, &ds->ctr_total, nullptr, st));
+            fill_pairs_kernel<Real><<<gn, 256, 0, st>>>(rec[nw], cell_start, pid[nw], n32, k, ctr_off, pairs, pairs_cap, ds);
+            *launches += 5;
         }
-        fill_contacts_kernel<Real><<<gn, 256, 0, st>>>(rec, cell_start, sorted_id, cell_id, n32, k, inc_off, entries, entries_cap,
-                                                       head, capture ? ctr_off : nullptr, capture ? pairs : nullptr, pairs_cap, ds);
         {
-            Rec<Real>* a_rec = rec; const uint32_t* a_off = inc_off; const uint32_t* a_ent = entries;
+            Rec<Real>* a_rec = rec[nw]; const uint32_t* a_end = list_end; const uint32_t* a_ent = entries;
             unsigned long long* a_head = head; uint32_t *a0 = wl[0], *a1 = wl[1], *a2 = wl[2];
-            uint32_t a_n = n32; StepConst<Real> a_k = k; DevState* a_ds = ds;
-            void* args[] = {&a_rec, &a_off, &a_ent, &a_head, &a0, &a1, &a2, &a_n, &a_k, &a_ds};
-            const uint64_t want = (n + 255) / 256;
+            StepConst<Real> a_k = k; DevState* a_ds = ds;
+            void* args[] = {&a_rec, &a_end, &a_ent, &a_head, &a0, &a1, &a2, &a_k, &a_ds};
+            const uint64_t want = (n + RESOLVE_THREADS - 1) / RESOLVE_THREADS;
             const unsigned grid = (unsigned)(want < (uint64_t)resolve_grid ? want : (uint64_t)resolve_grid);
-            PS_CUDA_TRY(err, cudaLaunchCooperativeKernel((const void*)resolve_kernel<Real>, dim3(grid), dim3(256), args, 0, st));
+            PS_CUDA_TRY(err, cudaLaunchCooperativeKernel((const void*)resolve_kernel<Real>, dim3(grid), dim3(RESOLVE_THREADS), args, 0, st));
+            ++*launches;
         }
-        scatter_back_kernel<Real><<<gn, 256, 0, st>>>(sorted_id, rec, n32, px, py, vx, vy);
         PS_CUDA_TRY(err, cudaGetLastError());
-        *launches += 13 + (capture ? 3 : 0);   // bin, 3+3 scan, place, rank, count, fill, resolve, scatter-back (+3 scan when capturing)
+        cur = nw;
         return PS_OK;
     }
 
