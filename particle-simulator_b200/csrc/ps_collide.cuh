@@ -257,26 +257,71 @@ __device__ __forceinline__ void walk_contacts(uint32_t a, const Rec<Real>* __res
     if (s.right) seg(s.r0, s.r1, 4u, 0u);
 }
 
-// One kernel builds every particle's contact sub-list: count, CTA-wide scan, one atomic per CTA
-// reserves the CTA's range of `entries`, second walk fills it.  Also seeds the first work list.
+// Per-particle cursor word, one 64-bit value so that a reader always sees a consistent snapshot:
+//   bits 63..45  stamp  = 1 + round of the last advance (0 = not advanced yet)
+//   bits 44..32  rem    = entries of this particle's sub-list not yet executed (<= 8191)
+//   bits 31..0   cursor = index in `entries` of the sub-list's current head
+constexpr int HEAD_REM_BITS = 13;
+constexpr uint32_t HEAD_REM_MAX = (1u << HEAD_REM_BITS) - 1;
+constexpr uint32_t HEAD_STAMP_MAX = (1u << (32 - HEAD_REM_BITS)) - 1;
+__host__ __device__ __forceinline__ unsigned long long head_word(uint32_t stamp, uint32_t rem, uint32_t cursor) {
+    return ((unsigned long long)stamp << (32 + HEAD_REM_BITS)) | ((unsigned long long)rem << 32) | cursor;
+}
+__device__ __forceinline__ uint32_t head_stamp(unsigned long long h) { return (uint32_t)(h >> (32 + HEAD_REM_BITS)); }
+__device__ __forceinline__ uint32_t head_rem(unsigned long long h) { return (uint32_t)(h >> 32) & HEAD_REM_MAX; }
+__device__ __forceinline__ uint32_t head_cursor(unsigned long long h) { return (uint32_t)h; }
+
+// One kernel builds every particle's contact sub-list.  Each candidate of the 3x3 block is tested
+// ONCE (three flat loops over the contiguous slot ranges of the left, own and right column) and the
+// hits are kept as a 64-bit mask; after a CTA-wide scan and one atomic per CTA that reserves the
+// CTA's range of `entries`, the mask is replayed in the reference's list order without touching
+// memory again.  A particle with more than 64 candidates takes the generic two-walk path.
+// Also seeds the first work list with {slot, first entry}.
 template <class Real>
 __global__ void __launch_bounds__(256)
 detect_kernel(const Rec<Real>* __restrict__ rec, const uint32_t* __restrict__ cell_start, uint32_t n, StepConst<Real> k,
               uint32_t* __restrict__ entries, uint32_t entries_cap, unsigned long long* __restrict__ head,
-              uint32_t* __restrict__ list_end, uint32_t* __restrict__ wl0, DevState* __restrict__ ds) {
+              uint2* __restrict__ wl0, DevState* __restrict__ ds) {
     __shared__ uint32_t sh_base, sh_wbase;
     const uint32_t a = blockIdx.x * blockDim.x + threadIdx.x;
     const bool valid = a < n;
     if (ds->flags) {                                         // error state (uniform: set by an earlier launch): no lists, no resolve
-        if (valid) { head[a] = 0ull; list_end[a] = 0u; }
+        if (valid) head[a] = 0ull;
         return;
     }
     Stencil st{};
-    uint32_t cnt = 0;
+    uint32_t cnt = 0, nL = 0, nM = 0, nR = 0;
+    unsigned long long mask = 0ull;
+    bool wide = false;
     if (valid) {
         const auto pa = ld_pos(rec + a);
         st = load_stencil<Real>(cell_start, cell_of<Real>(pa.x, pa.y, k), k);
-        walk_contacts<Real>(a, rec, st, k.r2sq, [&](uint32_t, uint32_t, uint32_t) { ++cnt; });
+        nL = st.left ? st.l3 - st.l0 : 0u;
+        nM = st.m3 - st.m0;
+        nR = st.right ? st.r3 - st.r0 : 0u;
+        wide = nL + nM + nR > 64u;
+        if (!wide) {
+            // checkCollision (:339-346); (xj-xi)^2 does not depend on which of the two is i, so one test serves both roles
+            const Real r2sq = k.r2sq;
+            uint32_t bit = 0;
+            auto test = [&](uint32_t b, uint32_t e) {
+                for (uint32_t q = b; q < e; ++q, ++bit) {
+                    const auto pq = ld_pos(rec + q);
+                    const Real dx = pq.x - pa.x, dy = pq.y - pa.y;
+                    const Real d2 = dx * dx + dy * dy;
+                    if (d2 < r2sq && q != a) mask |= 1ull << bit;
+                }
+            };
+            if (st.left) test(st.l0, st.l3);
+            test(st.m0, st.m3);
+            if (st.right) test(st.r0, st.r3);
+            // own-cell partners appear twice in a's sub-list (a as neighbour and a as centre, Q1)
+            const uint32_t own_off = nL + (st.m1 - st.m0), own_len = st.m2 - st.m1;
+            const unsigned long long own = own_len ? (((own_len >= 64u ? ~0ull : ((1ull << own_len) - 1ull)) << own_off) & mask) : 0ull;
+            cnt = (uint32_t)__popcll(mask) + (uint32_t)__popcll(own);
+        } else {
+            walk_contacts<Real>(a, rec, st, k.r2sq, [&](uint32_t, uint32_t, uint32_t) { ++cnt; });
+        }
     }
     // packed CTA scan: entry count in the low 22 bits, "has a list" flag above
     const uint32_t packed = cnt | ((cnt ? 1u : 0u) << 22);
@@ -291,19 +336,43 @@ detect_kernel(const Rec<Real>* __restrict__ rec, const uint32_t* __restrict__ ce
     if (!valid) return;
     const uint32_t te = total & ((1u << 22) - 1);
     const uint32_t begin = sh_base + (ex & ((1u << 22) - 1));
-    if ((uint64_t)sh_base + te > entries_cap) {                  // does not fit: flag; the resolve kernel will not run
-        if (threadIdx.x == 0) atomicOr(&ds->flags, FLAG_CAPACITY);
-        head[a] = 0ull; list_end[a] = 0u;
+    if ((uint64_t)sh_base + te > entries_cap || cnt > HEAD_REM_MAX) {   // does not fit: flag; the resolve kernel will not run
+        atomicOr(&ds->flags, FLAG_CAPACITY);
+        head[a] = 0ull;
         return;
     }
-    head[a] = (unsigned long long)begin;                         // high word: 1 + round of the last advance (0 = none yet)
-    list_end[a] = begin + cnt;
-    if (cnt) {
-        wl0[sh_wbase + (ex >> 22)] = a;
-        uint32_t w = begin;
+    head[a] = head_word(0u, cnt, begin);
+    if (!cnt) return;
+    uint32_t w = begin;
+    if (!wide) {
+        // replay the mask in list order; bit offset of slot q: left column q - l0, own column nL + q - m0, right column nL + nM + q - r0
+        auto emit = [&](uint32_t b, uint32_t e, uint32_t off, uint32_t o, uint32_t centre) {
+            if (e <= b) return;
+            const uint32_t len = e - b;
+            unsigned long long bits = (mask >> off) & (len >= 64u ? ~0ull : ((1ull << len) - 1ull));
+            while (bits) {
+                const uint32_t j = (uint32_t)__ffsll((long long)bits) - 1u;
+                bits &= bits - 1ull;
+                entries[w++] = make_entry(b + j, o, centre);
+            }
+        };
+        const uint32_t oM = nL - st.m0, oR = nL + nM - st.r0;          // wrap-around arithmetic: offset = oX + q
+        if (st.left) { emit(st.l0, st.l1, 0u, 3u, 0u); emit(st.l1, st.l2, st.l1 - st.l0, 2u, 0u); }
+        emit(st.m0, st.m1, oM + st.m0, 1u, 0u);
+        emit(st.m1, a, oM + st.m1, 0u, 0u);
+        emit(st.m1, a, oM + st.m1, 0u, 1u);
+        emit(a + 1, st.m2, oM + a + 1, 0u, 1u);
+        emit(st.m2, st.m3, oM + st.m2, 1u, 1u);
+        if (st.right) { emit(st.r1, st.r2, oR + st.r1, 2u, 1u); emit(st.r2, st.r3, oR + st.r2, 3u, 1u); }
+        if (st.left) emit(st.l2, st.l3, st.l2 - st.l0, 4u, 1u);
+        emit(a + 1, st.m2, oM + a + 1, 0u, 0u);
+        if (st.right) emit(st.r0, st.r1, oR + st.r0, 4u, 0u);
+    } else {
         walk_contacts<Real>(a, rec, st, k.r2sq, [&](uint32_t q, uint32_t o, uint32_t centre) { entries[w++] = make_entry(q, o, centre); });
     }
+    wl0[sh_wbase + (ex >> 22)] = make_uint2(a, entries[begin]);
 }
+
 
 // Pair capture (ps_capture_pairs): the global ordered list {particle_i, particle_j} (src/core.zig:203).
 template <class Real>
@@ -364,78 +433,103 @@ __device__ __forceinline__ void resolve_pair(Rec<Real>& I, Rec<Real>& J, const S
 }
 
 constexpr int RESOLVE_THREADS = 256;
+constexpr uint32_t RESOLVE_TAIL = 2048;   // work lists this short are finished by one CTA with CTA barriers only
+
+// One round over the work list `wl[0..cnt)`: every item {a, ea} is a particle whose head moved in the
+// previous round (or any particle with a list when r = 0) together with its head entry.  Appends the
+// particles advanced in this round, with their new head entry, to `out`.
+template <class Real>
+__device__ __forceinline__ void resolve_round(Rec<Real>* rec, const uint32_t* __restrict__ entries, unsigned long long* head,
+                                              const uint2* wl, uint32_t cnt, uint2* out, uint32_t* out_count, uint32_t r,
+                                              uint32_t first, uint32_t stride, const StepConst<Real>& k,
+                                              uint2* sh_buf, uint32_t* sh_cnt, uint32_t* sh_base) {
+    for (uint32_t base = first; base < cnt; base += stride) {
+        if (threadIdx.x == 0) *sh_cnt = 0;
+        __syncthreads();
+        const uint32_t idx = base + threadIdx.x;
+        do {
+            if (idx >= cnt) break;
+            const uint2 item = __ldcg(wl + idx);
+            const uint32_t a = item.x, ea = item.y;
+            const uint32_t b = ea & ENT_SLOT_MASK;
+            // everything that depends only on the item is requested at once (the records speculatively)
+            const unsigned long long ha = __ldcg(head + a);
+            const unsigned long long hb = __ldcg(head + b);
+            const Rec<Real> Ra = ld_rec_cg(rec + a), Rb = ld_rec_cg(rec + b);
+            if (head_stamp(ha) == r + 1) break;              // a already ran a pair this round (executed by its partner)
+            if (head_stamp(hb) == r + 1) break;              // b moved this round; b is on the next list and will look at a
+            const uint32_t rem_a = head_rem(ha), rem_b = head_rem(hb);
+            if (rem_b == 0) break;                           // (rem_a > 0: a is on the list)
+            const uint32_t ia = head_cursor(ha), ib = head_cursor(hb);
+            const uint32_t eb = entries[ib];
+            const uint32_t ea_next = rem_a > 1 ? entries[ia + 1] : 0u;
+            const uint32_t eb_next = rem_b > 1 ? entries[ib + 1] : 0u;
+            // same pair seen from the other side: partner = a, same offset, opposite role
+            if (eb != (a | (ea & (7u << 28)) | (~ea & (1u << 31)))) break;
+            // Both particles on this round's list (b's head last moved in round r-1, or never when r = 0): the
+            // lower slot runs the pair.  Membership is read from the SAME 64-bit word as the cursor, so a
+            // concurrent executor cannot make the two threads disagree.
+            if (b < a && head_stamp(hb) == r) break;
+            const bool a_centre = (ea >> 31) != 0;           // entry = {particle_i = neighbour, particle_j = centre}
+            Rec<Real> I = a_centre ? Rb : Ra, J = a_centre ? Ra : Rb;
+            resolve_pair<Real>(I, J, k);
+            st_rec(rec + (a_centre ? b : a), I);
+            st_rec(rec + (a_centre ? a : b), J);
+            head[a] = head_word(r + 1, rem_a - 1, ia + 1);
+            head[b] = head_word(r + 1, rem_b - 1, ib + 1);
+            if (rem_a > 1) sh_buf[atomicAdd(sh_cnt, 1u)] = make_uint2(a, ea_next);
+            if (rem_b > 1) sh_buf[atomicAdd(sh_cnt, 1u)] = make_uint2(b, eb_next);
+        } while (false);
+        __syncthreads();
+        const uint32_t m = *sh_cnt;
+        if (m) {                                             // one global atomic per CTA per batch
+            if (threadIdx.x == 0) *sh_base = atomicAdd(out_count, m);
+            __syncthreads();
+            for (uint32_t i = threadIdx.x; i < m; i += RESOLVE_THREADS) out[*sh_base + i] = sh_buf[i];
+        }
+        __syncthreads();
+    }
+}
 
 template <class Real>
 __global__ void __launch_bounds__(RESOLVE_THREADS)
-resolve_kernel(Rec<Real>* rec, const uint32_t* __restrict__ list_end, const uint32_t* __restrict__ entries,
-               unsigned long long* head, uint32_t* wl0, uint32_t* wl1, uint32_t* wl2, StepConst<Real> k, DevState* ds) {
+resolve_kernel(Rec<Real>* rec, const uint32_t* __restrict__ entries, unsigned long long* head,
+               uint2* wl0, uint2* wl1, uint2* wl2, StepConst<Real> k, DevState* ds) {
     cg::grid_group grid = cg::this_grid();
-    __shared__ uint32_t sh_buf[2 * RESOLVE_THREADS];
+    __shared__ uint2 sh_buf[2 * RESOLVE_THREADS];
     __shared__ uint32_t sh_cnt, sh_base;
-    uint32_t* lists[3] = {wl0, wl1, wl2};
+    uint2* lists[3] = {wl0, wl1, wl2};
     const bool leader = blockIdx.x == 0 && threadIdx.x == 0;
     if (ds->flags) {                                         // uniform across the grid: set before this launch
         if (leader) ds->wl_count[0] = 0;
         return;
     }
     uint32_t r = 0;
+    // grid phase: long work lists, one grid barrier per round
     for (;; ++r) {
         const uint32_t cur = r % 3, nxt = (r + 1) % 3, nn = (r + 2) % 3;
         const uint32_t cnt = __ldcg(&ds->wl_count[cur]);
-        if (cnt == 0) break;
+        if (cnt <= RESOLVE_TAIL) break;                      // same value in every thread: the whole grid leaves together
         if (leader) ds->wl_count[nn] = 0;                    // consumed in round r-1, refilled in round r+1
-        const uint32_t* wl = lists[cur];
-        uint32_t* out = lists[nxt];
-        for (uint32_t base = blockIdx.x * RESOLVE_THREADS; base < cnt; base += gridDim.x * RESOLVE_THREADS) {
-            if (threadIdx.x == 0) sh_cnt = 0;
-            __syncthreads();
-            const uint32_t idx = base + threadIdx.x;
-            do {
-                if (idx >= cnt) break;
-                const uint32_t a = __ldcg(wl + idx);
-                const unsigned long long ha = __ldcg(head + a);
-                if ((uint32_t)(ha >> 32) == r + 1) break;        // a already ran a pair this round (executed by its partner)
-                const uint32_t ia = (uint32_t)ha;
-                const uint32_t end_a = list_end[a];
-                if (ia >= end_a) break;                          // a's list is finished
-                const uint32_t ea = entries[ia];
-                const uint32_t b = ea & ENT_SLOT_MASK;
-                const unsigned long long hb = __ldcg(head + b);
-                if ((uint32_t)(hb >> 32) == r + 1) break;        // b moved this round; b is on the next list and will look at a
-                const uint32_t ib = (uint32_t)hb;
-                const uint32_t end_b = list_end[b];
-                if (ib >= end_b) break;
-                const uint32_t eb = entries[ib];
-                // same pair seen from the other side: partner = a, same offset, opposite role
-                if (eb != (a | (ea & (7u << 28)) | (~ea & (1u << 31)))) break;
-                // Both particles on this round's list (b's head last moved in round r-1, or never when r = 0): the
-                // lower slot runs the pair.  Membership is read from the SAME 64-bit word as the head index, so a
-                // concurrent executor cannot make the two threads disagree.
-                if (b < a && (uint32_t)(hb >> 32) == r) break;
-                const bool a_centre = (ea >> 31) != 0;
-                const uint32_t si = a_centre ? b : a, sj = a_centre ? a : b;   // entry = {particle_i = neighbour, particle_j = centre}
-                Rec<Real> I = ld_rec_cg(rec + si), J = ld_rec_cg(rec + sj);
-                resolve_pair<Real>(I, J, k);
-                st_rec(rec + si, I);
-                st_rec(rec + sj, J);
-                const unsigned long long stamp = (unsigned long long)(r + 1) << 32;
-                head[a] = stamp | (ia + 1);
-                head[b] = stamp | (ib + 1);
-                if (ia + 1 < end_a) sh_buf[atomicAdd(&sh_cnt, 1u)] = a;
-                if (ib + 1 < end_b) sh_buf[atomicAdd(&sh_cnt, 1u)] = b;
-            } while (false);
-            __syncthreads();
-            const uint32_t m = sh_cnt;
-            if (m) {                                             // one global atomic per CTA per batch
-                if (threadIdx.x == 0) sh_base = atomicAdd(&ds->wl_count[nxt], m);
-                __syncthreads();
-                for (uint32_t i = threadIdx.x; i < m; i += RESOLVE_THREADS) out[sh_base + i] = sh_buf[i];
-            }
-            __syncthreads();
-        }
+        resolve_round<Real>(rec, entries, head, lists[cur], cnt, lists[nxt], &ds->wl_count[nxt], r,
+                            blockIdx.x * RESOLVE_THREADS, gridDim.x * RESOLVE_THREADS, k, sh_buf, &sh_cnt, &sh_base);
         grid.sync();
     }
-    if (leader) {
+    if (blockIdx.x != 0) return;
+    // tail phase: CTA 0 alone, CTA barriers only (its own writes reach L2 before the barrier releases)
+    for (;; ++r) {
+        const uint32_t cur = r % 3, nxt = (r + 1) % 3, nn = (r + 2) % 3;
+        const uint32_t cnt = __ldcg(&ds->wl_count[cur]);
+        if (cnt == 0 || r + 2 >= HEAD_STAMP_MAX) break;
+        __syncthreads();                                     // everyone has read cnt before the counters move on
+        if (threadIdx.x == 0) ds->wl_count[nn] = 0;
+        resolve_round<Real>(rec, entries, head, lists[cur], cnt, lists[nxt], &ds->wl_count[nxt], r,
+                            0u, RESOLVE_THREADS, k, sh_buf, &sh_cnt, &sh_base);
+        __threadfence();
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        if (ds->wl_count[r % 3] != 0) atomicOr(&ds->flags, FLAG_CAPACITY);   // ran out of round stamps (never in practice)
         ds->rounds_last = r;
         ds->rounds_total += r;
         ds->inc_total = ds->entries_used;
@@ -443,6 +537,7 @@ resolve_kernel(Rec<Real>* rec, const uint32_t* __restrict__ list_end, const uint
         ds->wl_count[0] = ds->wl_count[1] = ds->wl_count[2] = 0;
     }
 }
+
 
 // ---- host side ---------------------------------------------------------------------------------
 template <class Real>
@@ -460,10 +555,10 @@ struct Collider {
     uint32_t *slot_cell = nullptr, *arrival = nullptr, *tmp_id = nullptr;
     Rec<Real>* rec[2] = {nullptr, nullptr};
     uint32_t* pid[2] = {nullptr, nullptr};
-    uint32_t *list_end = nullptr, *ctr_count = nullptr, *ctr_off = nullptr;
+    uint32_t *ctr_count = nullptr, *ctr_off = nullptr;
     uint32_t* entries = nullptr; uint32_t entries_cap = 0;
     unsigned long long* head = nullptr;
-    uint32_t* wl[3] = {nullptr, nullptr, nullptr};
+    uint2* wl[3] = {nullptr, nullptr, nullptr};
     uint64_t* pairs = nullptr; uint32_t pairs_cap = 0;
     DevState* ds = nullptr;
 
@@ -491,7 +586,6 @@ struct Collider {
             if ((rc = alloc(&rec[i], n, err))) return rc;
             if ((rc = alloc(&pid[i], n, err))) return rc;
         }
-        if ((rc = alloc(&list_end, n, err))) return rc;
         if ((rc = alloc(&entries, (uint64_t)entries_cap, err))) return rc;
         if ((rc = alloc(&head, n, err))) return rc;
         for (int i = 0; i < 3; ++i) if ((rc = alloc(&wl[i], n, err))) return rc;
@@ -509,7 +603,7 @@ struct Collider {
 
     void destroy() {
         cudaFree(cell_count); cudaFree(cell_start); cudaFree(scan_sums); cudaFree(slot_cell); cudaFree(arrival);
-        cudaFree(tmp_id); cudaFree(list_end); cudaFree(ctr_count); cudaFree(ctr_off); cudaFree(entries); cudaFree(head);
+        cudaFree(tmp_id); cudaFree(ctr_count); cudaFree(ctr_off); cudaFree(entries); cudaFree(head);
         for (auto& r : rec) cudaFree(r);
         for (auto& p : pid) cudaFree(p);
         for (auto& w : wl) cudaFree(w);
@@ -559,7 +653,7 @@ struct Collider {
         PS_CUDA_TRY(err, exclusive_scan_u32(cell_count, cell_start, ncell, scan_sums, cell_start + ncell, &ds->max_cell, st));
         place_kernel<<<gn, 256, 0, st>>>(slot_cell, arrival, pid[cur], cell_start, n32, tmp_id);
         move_kernel<Real><<<gn, 256, 0, st>>>(rec[cur], pid[cur], slot_cell, cell_start, tmp_id, n32, k, rec[nw], pid[nw], ds);
-        detect_kernel<Real><<<gn, 256, 0, st>>>(rec[nw], cell_start, n32, k, entries, entries_cap, head, list_end, wl[0], ds);
+        detect_kernel<Real><<<gn, 256, 0, st>>>(rec[nw], cell_start, n32, k, entries, entries_cap, head, wl[0], ds);
         *launches += 7;
         if (capture) {
             count_centre_kernel<Real><<<gn, 256, 0, st>>>(rec[nw], cell_start, n32, k, ctr_count);
@@ -568,10 +662,10 @@ struct Collider {
             *launches += 5;
         }
         {
-            Rec<Real>* a_rec = rec[nw]; const uint32_t* a_end = list_end; const uint32_t* a_ent = entries;
-            unsigned long long* a_head = head; uint32_t *a0 = wl[0], *a1 = wl[1], *a2 = wl[2];
+            Rec<Real>* a_rec = rec[nw]; const uint32_t* a_ent = entries;
+            unsigned long long* a_head = head; uint2 *a0 = wl[0], *a1 = wl[1], *a2 = wl[2];
             StepConst<Real> a_k = k; DevState* a_ds = ds;
-            void* args[] = {&a_rec, &a_end, &a_ent, &a_head, &a0, &a1, &a2, &a_k, &a_ds};
+            void* args[] = {&a_rec, &a_ent, &a_head, &a0, &a1, &a2, &a_k, &a_ds};
             const uint64_t want = (n + RESOLVE_THREADS - 1) / RESOLVE_THREADS;
             const unsigned grid = (unsigned)(want < (uint64_t)resolve_grid ? want : (uint64_t)resolve_grid);
             PS_CUDA_TRY(err, cudaLaunchCooperativeKernel((const void*)resolve_kernel<Real>, dim3(grid), dim3(RESOLVE_THREADS), args, 0, st));
