@@ -41,7 +41,8 @@ typedef enum ps_status {
     PS_ERR_NCCL = -4,          /* reserved for the multi-GPU slab path */
     PS_ERR_CELL_OVERFLOW = -5, /* a grid cell held > 255 particles: the reference's u8 counter would wrap or panic (src/core.zig:51,132) */
     PS_ERR_CAPACITY = -6,      /* contact list larger than the configured capacity; state is left at the failing sub-step's post-bounce point */
-    PS_ERR_NO_DEVICE = -7      /* no CUDA device / library built without one: the product has no CPU path */
+    PS_ERR_NO_DEVICE = -7,     /* no CUDA device / library built without one: the product has no CPU path */
+    PS_ERR_MIGRATION = -8      /* slab path: a particle crossed a whole neighbouring slab in one sub-step */
 } ps_status;
 
 typedef enum ps_precision {
@@ -183,6 +184,33 @@ int ps_compute_start_array(const uint32_t* grid_array, uint32_t* start_array, ui
  *     or different threads — race on it and both results are undefined.  Calls on one stream are safe.
  * Inputs and outputs are the caller's, as for ps_compute_start_array; in-place use is allowed. */
 int ps_compute_start_array_static(const uint32_t* grid_array, uint32_t* start_array, uint64_t cells, void* cuda_stream);
+
+/* ---- one scene across the GPUs of one box (collision scenes) ------------------------
+ * No counterpart in the reference (single process, single thread).  One process per GPU; rank k owns
+ * the particles whose grid column (src/core.zig:104) lies in its slab of whole cell columns and
+ * exchanges migrants, a one-column halo and the boundary particles' states with its x-neighbours by
+ * NCCL send/recv.  Results are those of ps_step on one GPU, bit for bit.  `cfg` describes the WHOLE
+ * scene (count = all particles) on every rank; cfg->collisions must be 1. */
+typedef struct ps_slab ps_slab;
+/* ncclGetUniqueId: rank 0 calls it and hands the 128 bytes to every rank (any host-side channel). */
+int ps_nccl_unique_id(void* id128);
+int ps_slab_create(const ps_config* cfg, int rank, int nranks, const void* nccl_id128, ps_slab** out);
+void ps_slab_destroy(ps_slab* slab);
+/* Spawner.spawnRandom (src/core.zig:395-410): every rank passes the same global arrays and keeps its slab. */
+int ps_slab_upload_global(ps_slab* slab, const double* pos_xy, const double* vel_xy);
+/* The same distribution generated on the device by the counter-based generator of scenes.py (no host arrays). */
+int ps_slab_spawn(ps_slab* slab, uint64_t seed, double vel_min, double vel_max);
+int ps_slab_step(ps_slab* slab, uint64_t frames);              /* Solver.updatePhysics x frames, this rank's share */
+int ps_slab_step_substeps(ps_slab* slab, uint64_t substeps);
+int ps_slab_set_acc(ps_slab* slab, int on);                    /* Solver.t_acc; must be set identically on all ranks */
+int ps_slab_sync(ps_slab* slab);
+int ps_slab_set_stream(ps_slab* slab, void* cuda_stream);
+int ps_slab_columns(const ps_slab* slab, uint64_t* x0, uint64_t* x1);   /* own grid columns [x0, x1) */
+int ps_slab_owned_count(ps_slab* slab, uint64_t* count);
+/* This rank's particles: original indices plus interleaved (x,y) positions and velocities. */
+int ps_slab_download_owned(ps_slab* slab, uint64_t* ids, double* pos_xy, double* vel_xy, uint64_t cap, uint64_t* count);
+int ps_slab_get_stats(ps_slab* slab, ps_stats* out);           /* pairs_* count the pairs whose centre this rank owns */
+const char* ps_slab_last_error(const ps_slab* slab);
 
 #ifdef __cplusplus
 }

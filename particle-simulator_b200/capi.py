@@ -18,6 +18,7 @@ PS_ERR_NCCL = -4
 PS_ERR_CELL_OVERFLOW = -5
 PS_ERR_CAPACITY = -6
 PS_ERR_NO_DEVICE = -7
+PS_ERR_MIGRATION = -8
 
 PS_F64 = 0
 PS_F32 = 1
@@ -99,6 +100,21 @@ SYMBOLS = {
     "ps_integrate_bounce_f64": (ctypes.c_int, [_CFG, ctypes.c_int, _P, _P, _P, _P, _U64, _U64, _P]),
     "ps_compute_start_array": (ctypes.c_int, [_P, _P, _U64, _P]),
     "ps_compute_start_array_static": (ctypes.c_int, [_P, _P, _U64, _P]),
+    "ps_nccl_unique_id": (ctypes.c_int, [_P]),
+    "ps_slab_create": (ctypes.c_int, [_CFG, ctypes.c_int, ctypes.c_int, _P, _PP]),
+    "ps_slab_destroy": (None, [_P]),
+    "ps_slab_upload_global": (ctypes.c_int, [_P, _P, _P]),
+    "ps_slab_spawn": (ctypes.c_int, [_P, _U64, ctypes.c_double, ctypes.c_double]),
+    "ps_slab_step": (ctypes.c_int, [_P, _U64]),
+    "ps_slab_step_substeps": (ctypes.c_int, [_P, _U64]),
+    "ps_slab_set_acc": (ctypes.c_int, [_P, ctypes.c_int]),
+    "ps_slab_sync": (ctypes.c_int, [_P]),
+    "ps_slab_set_stream": (ctypes.c_int, [_P, _P]),
+    "ps_slab_columns": (ctypes.c_int, [_P, _PU64, _PU64]),
+    "ps_slab_owned_count": (ctypes.c_int, [_P, _PU64]),
+    "ps_slab_download_owned": (ctypes.c_int, [_P, _P, _P, _P, _U64, _PU64]),
+    "ps_slab_get_stats": (ctypes.c_int, [_P, ctypes.POINTER(PsStats)]),
+    "ps_slab_last_error": (ctypes.c_char_p, [_P]),
 }
 
 # not part of the stable ABI (tuning hooks used by bench.py --sweep)

@@ -327,3 +327,113 @@ class Spawner:
         par.colors[:] = hsv_to_rgba(hue, 1.0, 1.0, 255)
 
     spawn_random = spawnRandom
+
+
+class SlabSimulation:
+    """One rank of a collision scene decomposed into x-slabs across the GPUs of one box (ps_slab_*).
+
+    `scene` is the WHOLE scene on every rank.  `nccl_id` is the 128-byte id from ``SlabSimulation.unique_id()``
+    on rank 0, handed to all ranks by the host program (torch.distributed broadcast, a file, ...)."""
+
+    def __init__(self, scene: scenes.Scene, rank: int, nranks: int, nccl_id: bytes | None = None, *, precision: str = "f64",
+                 device: int = 0, contacts_per_particle: int = 0):
+        self._L = capi.load()
+        cfg = capi.PsConfig()
+        cfg.struct_size = ctypes.sizeof(capi.PsConfig)
+        cfg.device = device
+        cfg.count = scene.count
+        cfg.radius, cfg.width, cfg.height, cfg.grid_size = scene.radius, scene.width, scene.height, scene.grid_size
+        cfg.target_fps, cfg.sub_steps, cfg.g = scene.target_fps, scene.sub_steps, scene.g
+        cfg.boundary_damping, cfg.particle_damping = scene.boundary_damping, scene.particle_damping
+        cfg.precision = capi.PS_F64 if precision == "f64" else capi.PS_F32
+        cfg.collisions = 1
+        cfg.contacts_per_particle = contacts_per_particle
+        self.cfg, self.scene, self.rank, self.nranks = cfg, scene, rank, nranks
+        h = ctypes.c_void_p()
+        idbuf = ctypes.create_string_buffer(nccl_id, 128) if nccl_id is not None else None
+        rc = self._L.ps_slab_create(ctypes.byref(cfg), rank, nranks, idbuf, ctypes.byref(h))
+        if rc != capi.PS_OK:
+            raise capi.PsError(rc, (self._L.ps_slab_last_error(None) or b"").decode())
+        self._h = h
+
+    @staticmethod
+    def unique_id() -> bytes:
+        L = capi.load()
+        buf = ctypes.create_string_buffer(128)
+        rc = L.ps_nccl_unique_id(buf)
+        if rc != capi.PS_OK:
+            raise capi.PsError(rc, (L.ps_slab_last_error(None) or b"").decode())
+        return buf.raw
+
+    def _check(self, rc):
+        if rc != capi.PS_OK:
+            raise capi.PsError(rc, (self._L.ps_slab_last_error(self._h) or self._L.ps_status_string(rc) or b"").decode())
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.ps_slab_destroy(self._h)
+            self._h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def upload_global(self, pos: np.ndarray, vel: np.ndarray) -> None:
+        assert pos.dtype == np.float64 and vel.dtype == np.float64 and pos.shape == (self.scene.count, 2) == vel.shape
+        assert pos.flags.c_contiguous and vel.flags.c_contiguous
+        self._check(self._L.ps_slab_upload_global(self._h, ctypes.c_void_p(pos.ctypes.data), ctypes.c_void_p(vel.ctypes.data)))
+
+    def spawn(self, seed: int, vel_min: float | None = None, vel_max: float | None = None) -> None:
+        vmin = self.scene.vel_min if vel_min is None else vel_min
+        vmax = self.scene.vel_max if vel_max is None else vel_max
+        self._check(self._L.ps_slab_spawn(self._h, seed, vmin, vmax))
+
+    def step(self, frames: int = 1) -> None:
+        self._check(self._L.ps_slab_step(self._h, frames))
+
+    def step_substeps(self, substeps: int) -> None:
+        self._check(self._L.ps_slab_step_substeps(self._h, substeps))
+
+    def set_acc(self, on: bool) -> None:
+        self._check(self._L.ps_slab_set_acc(self._h, int(on)))
+
+    def sync(self) -> None:
+        self._check(self._L.ps_slab_sync(self._h))
+
+    def set_stream(self, cuda_stream: int | None) -> None:
+        self._check(self._L.ps_slab_set_stream(self._h, ctypes.c_void_p(cuda_stream or 0)))
+
+    def columns(self):
+        a, b = ctypes.c_uint64(), ctypes.c_uint64()
+        self._check(self._L.ps_slab_columns(self._h, ctypes.byref(a), ctypes.byref(b)))
+        return int(a.value), int(b.value)
+
+    def owned_count(self) -> int:
+        n = ctypes.c_uint64()
+        self._check(self._L.ps_slab_owned_count(self._h, ctypes.byref(n)))
+        return int(n.value)
+
+    def download_owned(self):
+        """(ids uint64 (m,), pos float64 (m, 2), vel float64 (m, 2)) of the particles this rank owns."""
+        m = self.owned_count()
+        ids = np.empty(max(m, 1), dtype=np.uint64)
+        pos = np.empty((max(m, 1), 2), dtype=np.float64)
+        vel = np.empty((max(m, 1), 2), dtype=np.float64)
+        cnt = ctypes.c_uint64()
+        self._check(self._L.ps_slab_download_owned(self._h, ctypes.c_void_p(ids.ctypes.data), ctypes.c_void_p(pos.ctypes.data),
+                                                   ctypes.c_void_p(vel.ctypes.data), max(m, 1), ctypes.byref(cnt)))
+        m = int(cnt.value)
+        return ids[:m], pos[:m], vel[:m]
+
+    def stats(self) -> dict:
+        s = capi.PsStats()
+        self._check(self._L.ps_slab_get_stats(self._h, ctypes.byref(s)))
+        return {k: int(getattr(s, k)) for k, _ in capi.PsStats._fields_ if k != "reserved"}

@@ -15,6 +15,7 @@
 #include "ps_collide.cuh"
 #include "ps_common.cuh"
 #include "ps_integrate.cuh"
+#include "ps_slab.cuh"
 #include "ps_transfer.cuh"
 
 using ps::Error;
@@ -296,6 +297,7 @@ const char* ps_status_string(int status) {
         case PS_ERR_CELL_OVERFLOW: return "grid cell holds more than 255 particles";
         case PS_ERR_CAPACITY: return "contact list capacity exceeded";
         case PS_ERR_NO_DEVICE: return "no CUDA device";
+        case PS_ERR_MIGRATION: return "a particle crossed a whole slab in one sub-step";
         default: return "unknown status";
     }
 }
@@ -436,6 +438,110 @@ int ps_compute_start_array(const uint32_t* grid_array, uint32_t* start_array, ui
     const cudaError_t f = cudaFreeAsync(sums, st);
     return (k == cudaSuccess && f == cudaSuccess) ? PS_OK : PS_ERR_CUDA;
 }
+
+// ---- slab-decomposed collision scenes (one process per GPU) ---------------------------------------------
+}  // extern "C"
+
+struct ps_slab {
+    virtual ~ps_slab() {}
+    virtual int upload_global(const double* pos, const double* vel) = 0;
+    virtual int spawn(uint64_t seed, double vmin, double vmax) = 0;
+    virtual int step(uint64_t substeps) = 0;
+    virtual int set_acc(bool on) = 0;
+    virtual int sync() = 0;
+    virtual int set_stream(void* st) = 0;
+    virtual int columns(uint64_t* x0, uint64_t* x1) const = 0;
+    virtual int owned_count(uint64_t* n) = 0;
+    virtual int download_owned(uint64_t* ids, double* pos, double* vel, uint64_t cap, uint64_t* count) = 0;
+    virtual int stats(ps_stats* out) = 0;
+    virtual const char* last_error() const = 0;
+    virtual uint64_t sub_steps() const = 0;
+};
+
+namespace {
+template <class Real>
+struct SlabT final : ps_slab {
+    ps::SlabCollider<Real> c;
+    ~SlabT() override { DeviceGuard g(c.device); c.destroy(); }
+    int upload_global(const double* pos, const double* vel) override { DeviceGuard g(c.device); return c.upload_global(pos, vel); }
+    int spawn(uint64_t seed, double vmin, double vmax) override { DeviceGuard g(c.device); return c.spawn(seed, vmin, vmax); }
+    int step(uint64_t substeps) override {
+        DeviceGuard g(c.device);
+        for (uint64_t s = 0; s < substeps; ++s) { const int rc = c.substep(); if (rc != PS_OK) return rc; }
+        return PS_OK;
+    }
+    int set_acc(bool on) override { c.t_acc = on; return PS_OK; }
+    int sync() override { DeviceGuard g(c.device); return c.sync(); }
+    int set_stream(void* st) override {
+        DeviceGuard g(c.device);
+        cudaStreamSynchronize(c.stream);
+        c.stream = st ? (cudaStream_t)st : c.own_stream;
+        return PS_OK;
+    }
+    int columns(uint64_t* x0, uint64_t* x1) const override { *x0 = c.g.x0; *x1 = c.g.x1; return PS_OK; }
+    int owned_count(uint64_t* n) override { DeviceGuard g(c.device); cudaStreamSynchronize(c.stream); *n = c.last.own_e - c.last.own_b; return PS_OK; }
+    int download_owned(uint64_t* ids, double* pos, double* vel, uint64_t cap, uint64_t* count) override {
+        DeviceGuard g(c.device);
+        return c.download_owned(ids, pos, vel, cap, count);
+    }
+    int stats(ps_stats* out) override { DeviceGuard g(c.device); return c.stats(out); }
+    const char* last_error() const override { return c.err.text.c_str(); }
+    uint64_t sub_steps() const override { return c.cfg.sub_steps; }
+};
+
+template <class Real>
+int slab_create_t(const ps_config* cfg, int rank, int nranks, const void* id, uint32_t rows, uint32_t cols, ps_slab** out) {
+    auto* s = new (std::nothrow) SlabT<Real>();
+    if (!s) { g_create_error = "host allocation failed"; return PS_ERR_OOM; }
+    DeviceGuard g(cfg->device);
+    const int rc = s->c.create(*cfg, rank, nranks, static_cast<const ps::NcclUniqueId*>(id), rows, cols);
+    if (rc != PS_OK) { g_create_error = s->c.err.text; delete s; return rc; }
+    *out = s;
+    return PS_OK;
+}
+}  // namespace
+
+extern "C" {
+
+int ps_nccl_unique_id(void* id128) {
+    if (!id128) return PS_ERR_BAD_ARG;
+    const ps::NcclApi& api = ps::nccl_api();
+    if (!api.ok) { g_create_error = api.error; return PS_ERR_NCCL; }
+    return api.GetUniqueId(static_cast<ps::NcclUniqueId*>(id128)) == ps::kNcclSuccess ? PS_OK : PS_ERR_NCCL;
+}
+
+int ps_slab_create(const ps_config* cfg, int rank, int nranks, const void* nccl_id128, ps_slab** out) {
+    if (!out) { g_create_error = "out is NULL"; return PS_ERR_BAD_ARG; }
+    *out = nullptr;
+    uint32_t rows = 0, cols = 0;
+    std::string why;
+    int rc = validate(cfg, &rows, &cols, &why);
+    if (rc != PS_OK) { g_create_error = "ps_slab_create: " + why; return rc; }
+    if (!cfg->collisions) { g_create_error = "ps_slab_create: slabs are for collision scenes (integration-only scenes shard by index, no exchange)"; return PS_ERR_BAD_ARG; }
+    if (nranks < 1 || rank < 0 || rank >= nranks) { g_create_error = "ps_slab_create: bad rank / nranks"; return PS_ERR_BAD_ARG; }
+    if (cfg->count >= (1ull << 32)) { g_create_error = "ps_slab_create: particle indices are 32-bit"; return PS_ERR_BAD_ARG; }
+    int ndev = 0;
+    const cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) { cudaGetLastError(); g_create_error = "ps_slab_create: no CUDA device; this library has no CPU path"; return PS_ERR_NO_DEVICE; }
+    if (cfg->device < 0 || cfg->device >= ndev) { g_create_error = "ps_slab_create: device ordinal out of range"; return PS_ERR_BAD_ARG; }
+    return cfg->precision == PS_F64 ? slab_create_t<double>(cfg, rank, nranks, nccl_id128, rows, cols, out)
+                                    : slab_create_t<float>(cfg, rank, nranks, nccl_id128, rows, cols, out);
+}
+void ps_slab_destroy(ps_slab* s) { delete s; }
+int ps_slab_upload_global(ps_slab* s, const double* pos, const double* vel) { return (s && pos && vel) ? s->upload_global(pos, vel) : PS_ERR_BAD_ARG; }
+int ps_slab_spawn(ps_slab* s, uint64_t seed, double vmin, double vmax) { return s ? s->spawn(seed, vmin, vmax) : PS_ERR_BAD_ARG; }
+int ps_slab_step(ps_slab* s, uint64_t frames) { return s ? s->step(frames * s->sub_steps()) : PS_ERR_BAD_ARG; }
+int ps_slab_step_substeps(ps_slab* s, uint64_t substeps) { return s ? s->step(substeps) : PS_ERR_BAD_ARG; }
+int ps_slab_set_acc(ps_slab* s, int on) { return s ? s->set_acc(on != 0) : PS_ERR_BAD_ARG; }
+int ps_slab_sync(ps_slab* s) { return s ? s->sync() : PS_ERR_BAD_ARG; }
+int ps_slab_set_stream(ps_slab* s, void* st) { return s ? s->set_stream(st) : PS_ERR_BAD_ARG; }
+int ps_slab_columns(const ps_slab* s, uint64_t* x0, uint64_t* x1) { return (s && x0 && x1) ? s->columns(x0, x1) : PS_ERR_BAD_ARG; }
+int ps_slab_owned_count(ps_slab* s, uint64_t* n) { return (s && n) ? s->owned_count(n) : PS_ERR_BAD_ARG; }
+int ps_slab_download_owned(ps_slab* s, uint64_t* ids, double* pos, double* vel, uint64_t cap, uint64_t* count) {
+    return (s && count) ? s->download_owned(ids, pos, vel, cap, count) : PS_ERR_BAD_ARG;
+}
+int ps_slab_get_stats(ps_slab* s, ps_stats* out) { return (s && out) ? s->stats(out) : PS_ERR_BAD_ARG; }
+const char* ps_slab_last_error(const ps_slab* s) { return s ? s->last_error() : g_create_error.c_str(); }
 
 // ---- ps_compute_start_array_static: the same prefix sum with no allocation anywhere ------------------
 //

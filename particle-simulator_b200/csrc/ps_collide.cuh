@@ -277,13 +277,35 @@ __device__ __forceinline__ uint32_t head_cursor(unsigned long long h) { return (
 // CTA's range of `entries`, the mask is replayed in the reference's list order without touching
 // memory again.  A particle with more than 64 candidates takes the generic two-walk path.
 // Also seeds the first work list with {slot, first entry}.
-template <class Real>
+//
+// Multi-GPU slabs (SLAB = true, ps_slab.cuh): the local grid has one ghost column on each side that
+// has a neighbour rank.  An entry is listed on this rank only if its CENTRE particle sits in an own
+// column (the pair list is ordered by centre, so a pair belongs to the rank that owns its centre);
+// particles of the first two local columns start "blocked" (their sub-list becomes visible only after
+// the left rank has handed over their state): their count goes to `brem`, their cursor word says 0 left.
+struct SlabView {
+    uint32_t gl, gr;          // 1 if a left / right ghost column exists
+    uint32_t ncl;             // local columns (own + ghosts)
+    uint32_t col_off;         // global column of local column 0
+    uint32_t gcols;           // global column count (clamp of computeCoordinate, src/core.zig:108)
+    const uint32_t* n_local;  // device: slots in use
+    const uint32_t* n_blocked;// device: slots of the first two local columns (0 when gl = 0)
+    uint32_t* brem;           // per slot: sub-list length of a blocked particle
+};
+
+__device__ __forceinline__ unsigned long long range_bits(unsigned long long mask, uint32_t off, uint32_t len) {
+    if (len == 0u) return 0ull;
+    return (mask >> off) & (len >= 64u ? ~0ull : ((1ull << len) - 1ull));
+}
+
+template <class Real, bool SLAB>
 __global__ void __launch_bounds__(256)
 detect_kernel(const Rec<Real>* __restrict__ rec, const uint32_t* __restrict__ cell_start, uint32_t n, StepConst<Real> k,
               uint32_t* __restrict__ entries, uint32_t entries_cap, unsigned long long* __restrict__ head,
-              uint2* __restrict__ wl0, DevState* __restrict__ ds) {
+              uint2* __restrict__ wl0, DevState* __restrict__ ds, SlabView sv) {
     __shared__ uint32_t sh_base, sh_wbase;
     const uint32_t a = blockIdx.x * blockDim.x + threadIdx.x;
+    if (SLAB) n = *sv.n_local;
     const bool valid = a < n;
     if (ds->flags) {                                         // error state (uniform: set by an earlier launch): no lists, no resolve
         if (valid) head[a] = 0ull;
@@ -292,10 +314,25 @@ detect_kernel(const Rec<Real>* __restrict__ rec, const uint32_t* __restrict__ ce
     Stencil st{};
     uint32_t cnt = 0, nL = 0, nM = 0, nR = 0;
     unsigned long long mask = 0ull;
-    bool wide = false;
+    bool wide = false, a_own = true, l_own = true, r_own = true, blocked = false;
     if (valid) {
         const auto pa = ld_pos(rec + a);
-        st = load_stencil<Real>(cell_start, cell_of<Real>(pa.x, pa.y, k), k);
+        uint32_t c;
+        if (SLAB) {
+            // local cell: global computeCoordinate, then shift by the slab's first local column
+            const Real fi = floor_r(div_rn(pa.x, k.grid_size)), fj = floor_r(div_rn(pa.y, k.grid_size));
+            const uint32_t gi = fi > (Real)0 ? (fi < (Real)sv.gcols ? (uint32_t)fi : sv.gcols - 1) : 0u;
+            const uint32_t gj = fj > (Real)0 ? (fj < (Real)k.rows ? (uint32_t)fj : k.rows - 1) : 0u;
+            const uint32_t lx = gi - sv.col_off;
+            c = lx * k.rows + gj;
+            a_own = lx >= sv.gl && lx < sv.ncl - sv.gr;
+            l_own = lx >= 1u && (lx - 1u) >= sv.gl && (lx - 1u) < sv.ncl - sv.gr;
+            r_own = (lx + 1u) >= sv.gl && (lx + 1u) < sv.ncl - sv.gr;
+            blocked = a < *sv.n_blocked;
+        } else {
+            c = cell_of<Real>(pa.x, pa.y, k);
+        }
+        st = load_stencil<Real>(cell_start, c, k);
         nL = st.left ? st.l3 - st.l0 : 0u;
         nM = st.m3 - st.m0;
         nR = st.right ? st.r3 - st.r0 : 0u;
@@ -316,15 +353,25 @@ detect_kernel(const Rec<Real>* __restrict__ rec, const uint32_t* __restrict__ ce
             test(st.m0, st.m3);
             if (st.right) test(st.r0, st.r3);
             // own-cell partners appear twice in a's sub-list (a as neighbour and a as centre, Q1)
-            const uint32_t own_off = nL + (st.m1 - st.m0), own_len = st.m2 - st.m1;
-            const unsigned long long own = own_len ? (((own_len >= 64u ? ~0ull : ((1ull << own_len) - 1ull)) << own_off) & mask) : 0ull;
-            cnt = (uint32_t)__popcll(mask) + (uint32_t)__popcll(own);
+            if (!SLAB) {
+                cnt = (uint32_t)__popcll(mask) + (uint32_t)__popcll(range_bits(mask, nL + (st.m1 - st.m0), st.m2 - st.m1));
+            } else {
+                if (l_own) cnt += (uint32_t)__popcll(range_bits(mask, 0u, st.l2 - st.l0));                       // a neighbour of left-column centres
+                if (r_own) cnt += (uint32_t)__popcll(range_bits(mask, nL + nM, st.r1 - st.r0));                  // ... of right-column centres
+                if (a_own) cnt += (uint32_t)__popcll(range_bits(mask, nL, nM))                                    // own column, both roles
+                                + (uint32_t)__popcll(range_bits(mask, nL + (st.m1 - st.m0), st.m2 - st.m1))       // own cell listed twice
+                                + (uint32_t)__popcll(range_bits(mask, nL + nM + (st.r1 - st.r0), st.r3 - st.r1))  // a centre, right column
+                                + (uint32_t)__popcll(range_bits(mask, st.l2 - st.l0, st.l3 - st.l2));             // a centre, (-1,1)
+            }
         } else {
-            walk_contacts<Real>(a, rec, st, k.r2sq, [&](uint32_t, uint32_t, uint32_t) { ++cnt; });
+            walk_contacts<Real>(a, rec, st, k.r2sq, [&](uint32_t, uint32_t o, uint32_t centre) {
+                const bool keep = !SLAB || (centre ? a_own : (o >= 2u && o <= 3u ? l_own : (o == 4u ? r_own : a_own)));
+                cnt += keep ? 1u : 0u;
+            });
         }
     }
-    // packed CTA scan: entry count in the low 22 bits, "has a list" flag above
-    const uint32_t packed = cnt | ((cnt ? 1u : 0u) << 22);
+    // packed CTA scan: entry count in the low 22 bits, "goes on the first work list" flag above
+    const uint32_t packed = cnt | (((cnt && !blocked) ? 1u : 0u) << 22);
     uint32_t total;
     const uint32_t ex = block_exclusive_scan<256>(packed, &total);
     if (threadIdx.x == 0) {
@@ -341,15 +388,15 @@ detect_kernel(const Rec<Real>* __restrict__ rec, const uint32_t* __restrict__ ce
         head[a] = 0ull;
         return;
     }
-    head[a] = head_word(0u, cnt, begin);
+    head[a] = head_word(0u, blocked ? 0u : cnt, begin);
+    if (SLAB) sv.brem[a] = blocked ? cnt : 0u;
     if (!cnt) return;
     uint32_t w = begin;
     if (!wide) {
         // replay the mask in list order; bit offset of slot q: left column q - l0, own column nL + q - m0, right column nL + nM + q - r0
         auto emit = [&](uint32_t b, uint32_t e, uint32_t off, uint32_t o, uint32_t centre) {
             if (e <= b) return;
-            const uint32_t len = e - b;
-            unsigned long long bits = (mask >> off) & (len >= 64u ? ~0ull : ((1ull << len) - 1ull));
+            unsigned long long bits = range_bits(mask, off, e - b);
             while (bits) {
                 const uint32_t j = (uint32_t)__ffsll((long long)bits) - 1u;
                 bits &= bits - 1ull;
@@ -357,20 +404,25 @@ detect_kernel(const Rec<Real>* __restrict__ rec, const uint32_t* __restrict__ ce
             }
         };
         const uint32_t oM = nL - st.m0, oR = nL + nM - st.r0;          // wrap-around arithmetic: offset = oX + q
-        if (st.left) { emit(st.l0, st.l1, 0u, 3u, 0u); emit(st.l1, st.l2, st.l1 - st.l0, 2u, 0u); }
-        emit(st.m0, st.m1, oM + st.m0, 1u, 0u);
-        emit(st.m1, a, oM + st.m1, 0u, 0u);
-        emit(st.m1, a, oM + st.m1, 0u, 1u);
-        emit(a + 1, st.m2, oM + a + 1, 0u, 1u);
-        emit(st.m2, st.m3, oM + st.m2, 1u, 1u);
-        if (st.right) { emit(st.r1, st.r2, oR + st.r1, 2u, 1u); emit(st.r2, st.r3, oR + st.r2, 3u, 1u); }
-        if (st.left) emit(st.l2, st.l3, st.l2 - st.l0, 4u, 1u);
-        emit(a + 1, st.m2, oM + a + 1, 0u, 0u);
-        if (st.right) emit(st.r0, st.r1, oR + st.r0, 4u, 0u);
+        if (st.left && l_own) { emit(st.l0, st.l1, 0u, 3u, 0u); emit(st.l1, st.l2, st.l1 - st.l0, 2u, 0u); }
+        if (a_own) {
+            emit(st.m0, st.m1, oM + st.m0, 1u, 0u);
+            emit(st.m1, a, oM + st.m1, 0u, 0u);
+            emit(st.m1, a, oM + st.m1, 0u, 1u);
+            emit(a + 1, st.m2, oM + a + 1, 0u, 1u);
+            emit(st.m2, st.m3, oM + st.m2, 1u, 1u);
+            if (st.right) { emit(st.r1, st.r2, oR + st.r1, 2u, 1u); emit(st.r2, st.r3, oR + st.r2, 3u, 1u); }
+            if (st.left) emit(st.l2, st.l3, st.l2 - st.l0, 4u, 1u);
+            emit(a + 1, st.m2, oM + a + 1, 0u, 0u);
+        }
+        if (st.right && r_own) emit(st.r0, st.r1, oR + st.r0, 4u, 0u);
     } else {
-        walk_contacts<Real>(a, rec, st, k.r2sq, [&](uint32_t q, uint32_t o, uint32_t centre) { entries[w++] = make_entry(q, o, centre); });
+        walk_contacts<Real>(a, rec, st, k.r2sq, [&](uint32_t q, uint32_t o, uint32_t centre) {
+            const bool keep = !SLAB || (centre ? a_own : (o >= 2u && o <= 3u ? l_own : (o == 4u ? r_own : a_own)));
+            if (keep) entries[w++] = make_entry(q, o, centre);
+        });
     }
-    wl0[sh_wbase + (ex >> 22)] = make_uint2(a, entries[begin]);
+    if (!blocked) wl0[sh_wbase + (ex >> 22)] = make_uint2(a, entries[begin]);
 }
 
 
@@ -494,7 +546,7 @@ __device__ __forceinline__ void resolve_round(Rec<Real>* rec, const uint32_t* __
 template <class Real>
 __global__ void __launch_bounds__(RESOLVE_THREADS)
 resolve_kernel(Rec<Real>* rec, const uint32_t* __restrict__ entries, unsigned long long* head,
-               uint2* wl0, uint2* wl1, uint2* wl2, StepConst<Real> k, DevState* ds) {
+               uint2* wl0, uint2* wl1, uint2* wl2, StepConst<Real> k, DevState* ds, uint32_t r_start) {
     cg::grid_group grid = cg::this_grid();
     __shared__ uint2 sh_buf[2 * RESOLVE_THREADS];
     __shared__ uint32_t sh_cnt, sh_base;
@@ -504,7 +556,7 @@ resolve_kernel(Rec<Real>* rec, const uint32_t* __restrict__ entries, unsigned lo
         if (leader) ds->wl_count[0] = 0;
         return;
     }
-    uint32_t r = 0;
+    uint32_t r = r_start;                                    // > 0 only for the second phase of a slab sub-step (ps_slab.cuh)
     // grid phase: long work lists, one grid barrier per round
     for (;; ++r) {
         const uint32_t cur = r % 3, nxt = (r + 1) % 3, nn = (r + 2) % 3;
@@ -531,9 +583,11 @@ resolve_kernel(Rec<Real>* rec, const uint32_t* __restrict__ entries, unsigned lo
     if (threadIdx.x == 0) {
         if (ds->wl_count[r % 3] != 0) atomicOr(&ds->flags, FLAG_CAPACITY);   // ran out of round stamps (never in practice)
         ds->rounds_last = r;
-        ds->rounds_total += r;
-        ds->inc_total = ds->entries_used;
-        ds->pairs_total += ds->entries_used / 2;
+        ds->rounds_total += r - r_start;
+        if (r_start == 0) {
+            ds->inc_total = ds->entries_used;
+            ds->pairs_total += ds->entries_used / 2;
+        }
         ds->wl_count[0] = ds->wl_count[1] = ds->wl_count[2] = 0;
     }
 }
@@ -653,7 +707,7 @@ struct Collider {
         PS_CUDA_TRY(err, exclusive_scan_u32(cell_count, cell_start, ncell, scan_sums, cell_start + ncell, &ds->max_cell, st));
         place_kernel<<<gn, 256, 0, st>>>(slot_cell, arrival, pid[cur], cell_start, n32, tmp_id);
         move_kernel<Real><<<gn, 256, 0, st>>>(rec[cur], pid[cur], slot_cell, cell_start, tmp_id, n32, k, rec[nw], pid[nw], ds);
-        detect_kernel<Real><<<gn, 256, 0, st>>>(rec[nw], cell_start, n32, k, entries, entries_cap, head, wl[0], ds);
+        detect_kernel<Real, false><<<gn, 256, 0, st>>>(rec[nw], cell_start, n32, k, entries, entries_cap, head, wl[0], ds, SlabView{});
         *launches += 7;
         if (capture) {
             count_centre_kernel<Real><<<gn, 256, 0, st>>>(rec[nw], cell_start, n32, k, ctr_count);
@@ -664,8 +718,8 @@ struct Collider {
         {
             Rec<Real>* a_rec = rec[nw]; const uint32_t* a_ent = entries;
             unsigned long long* a_head = head; uint2 *a0 = wl[0], *a1 = wl[1], *a2 = wl[2];
-            StepConst<Real> a_k = k; DevState* a_ds = ds;
-            void* args[] = {&a_rec, &a_ent, &a_head, &a0, &a1, &a2, &a_k, &a_ds};
+            StepConst<Real> a_k = k; DevState* a_ds = ds; uint32_t a_r0 = 0;
+            void* args[] = {&a_rec, &a_ent, &a_head, &a0, &a1, &a2, &a_k, &a_ds, &a_r0};
             const uint64_t want = (n + RESOLVE_THREADS - 1) / RESOLVE_THREADS;
             const unsigned grid = (unsigned)(want < (uint64_t)resolve_grid ? want : (uint64_t)resolve_grid);
             PS_CUDA_TRY(err, cudaLaunchCooperativeKernel((const void*)resolve_kernel<Real>, dim3(grid), dim3(RESOLVE_THREADS), args, 0, st));

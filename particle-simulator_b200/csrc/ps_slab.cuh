@@ -1,0 +1,641 @@
+// ps_slab.cuh — the collision step slab-decomposed across the GPUs of one box.
+//
+// One process per GPU.  Rank k owns the particles whose cell column lies in [x0, x1); cells are
+// column-major (src/core.zig:120), so a slab is a contiguous range of cell indices and the
+// reference's global pair list is slab-major: every pair belongs to the rank that owns its CENTRE
+// particle, and all of rank k's pairs precede all of rank k+1's.  Dependencies therefore cross a
+// slab boundary in one direction only, through the particles of the two columns next to it:
+//
+//   M0  (before detection, both ways)  migrants (particles whose new column left the slab) and the
+//       halo (own particles now in the boundary column), post-integrate state, with particle index.
+//       Each rank sorts own + ghost columns into its local grid; both ranks of a boundary hold the
+//       same particles of the two boundary columns in the same (cell, index) order.
+//   M1  (rightward)  after rank k has executed its pairs: the state of its last own column and of
+//       its right ghost column (= rank k+1's left ghost column and first own column, same order, so
+//       the message is one contiguous range of records).  Until M1 arrives rank k+1 keeps those
+//       particles "blocked": pairs that involve them wait, everything else proceeds (phase A); then
+//       it unblocks them and finishes (phase B).
+//   M2  (leftward)  the final state of rank k+1's left ghost column returns to rank k, which owns it.
+//
+// The result is bit-identical to the single-GPU / sequential reference order (the protocol is
+// modelled on the CPU in tests/_slab_model.py and checked against the oracle).  Transport is NCCL
+// ncclSend / ncclRecv between x-neighbours inside one ncclGroup per exchange (NVLink 5 / NVSwitch);
+// messages are a few hundred KB, so the cost is latency: one host synchronisation per sub-step.
+#pragma once
+#include <cstring>
+#include <vector>
+
+#include "ps_collide.cuh"
+#include "ps_nccl.h"
+
+namespace ps {
+
+constexpr uint32_t SLAB_INVALID = 0xffffffffu;
+constexpr uint32_t SLAB_ERR_MIGRATION = 1u;   // a particle crossed a whole neighbouring slab in one sub-step
+constexpr uint32_t SLAB_ERR_HALO = 2u;        // halo / migration buffer too small
+constexpr uint32_t SLAB_ERR_CAPACITY = 4u;    // more local particles than the handle was sized for
+constexpr uint32_t SLAB_ERR_PROTOCOL = 8u;    // boundary hand-over sizes disagree between ranks
+
+struct SlabGeom {
+    uint32_t rows, gcols;      // global grid
+    uint32_t x0, x1;           // own global columns [x0, x1)
+    uint32_t gl, gr;           // ghost column on the left / right
+    uint32_t col_off, ncl;     // local grid: global column of local column 0, number of local columns
+    uint32_t xlo, xhi;         // a particle of this rank may land in [xlo, xhi) (the neighbours' slabs)
+    uint32_t cap, cap_h;       // capacities: local particles, records per halo buffer
+};
+
+struct SlabDev {               // device-side counters, copied to the host once per sub-step
+    uint32_t n_local;          // slots in use (own + ghost columns)
+    uint32_t own_b, own_e;     // owned slot range
+    uint32_t c_first1, c_first2, c_last2, c_last1;   // cell_start at local columns 1, 2, ncl-2, ncl-1
+    uint32_t n_blocked;        // = c_first2 when a left neighbour exists, else 0
+    uint32_t right_incomplete; // some particle of the last two local columns still has pending pairs
+    uint32_t err;
+    uint32_t n_own_prev;       // owned particles at the start of this sub-step
+    uint32_t zero;             // always 0 (range start for the pack / unpack kernels)
+};
+
+// halo / migration message: header + records + particle indices
+struct HaloHeader { uint32_t count, pad0, pad1, pad2; };
+template <class Real> __host__ __device__ inline size_t halo_bytes(uint32_t cap_h) { return sizeof(HaloHeader) + (size_t)cap_h * (sizeof(Rec<Real>) + sizeof(uint32_t)); }
+template <class Real> __device__ __forceinline__ Rec<Real>* halo_recs(void* buf) { return reinterpret_cast<Rec<Real>*>(static_cast<char*>(buf) + sizeof(HaloHeader)); }
+template <class Real> __device__ __forceinline__ uint32_t* halo_pids(void* buf, uint32_t cap_h) {
+    return reinterpret_cast<uint32_t*>(static_cast<char*>(buf) + sizeof(HaloHeader) + (size_t)cap_h * sizeof(Rec<Real>));
+}
+
+template <class Real>
+__device__ __forceinline__ void global_cell(Real x, Real y, const StepConst<Real>& k, uint32_t gcols, uint32_t& gi, uint32_t& gj) {
+    const Real fi = floor_r(div_rn(x, k.grid_size)), fj = floor_r(div_rn(y, k.grid_size));   // computeCoordinate, src/core.zig:103-115
+    gi = fi > (Real)0 ? (fi < (Real)gcols ? (uint32_t)fi : gcols - 1) : 0u;
+    gj = fj > (Real)0 ? (fj < (Real)k.rows ? (uint32_t)fj : k.rows - 1) : 0u;
+}
+
+// ---- initial distribution -----------------------------------------------------------------------
+// Keep the particles of this rank's columns out of a chunk of the global arrays (original index = first + i).
+template <class Real>
+__global__ void __launch_bounds__(256)
+slab_filter_kernel(const double2* __restrict__ pos, const double2* __restrict__ vel, uint64_t first, uint32_t count,
+                   StepConst<Real> k, SlabGeom g, Rec<Real>* __restrict__ rec, uint32_t* __restrict__ pid, SlabDev* __restrict__ sd) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= count) return;
+    const double2 p = pos[i], v = vel[i];
+    const Rec<Real> r{(Real)p.x, (Real)p.y, (Real)v.x, (Real)v.y};
+    uint32_t gi, gj;
+    global_cell<Real>(r.x, r.y, k, g.gcols, gi, gj);
+    if (gi < g.x0 || gi >= g.x1) return;
+    const uint32_t s = atomicAdd(&sd->own_e, 1u);
+    if (s >= g.cap) { atomicOr(&sd->err, SLAB_ERR_CAPACITY); return; }
+    st_rec(rec + s, r);
+    pid[s] = (uint32_t)(first + i);
+}
+
+__device__ __forceinline__ uint64_t splitmix64_dev(uint64_t z) {
+    z += 0x9E3779B97F4A7C15ull;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return z ^ (z >> 31);
+}
+__device__ __forceinline__ double uniform01_dev(uint64_t base, uint64_t index, uint64_t stream) {
+    return (double)(splitmix64_dev((index * 4ull + stream) ^ base) >> 11) * (1.0 / 9007199254740992.0);
+}
+
+// Spawner.spawnRandom's distribution (src/core.zig:403-408) with the counter-based generator of scenes.py,
+// evaluated for every global index; a rank keeps what falls into its columns.  f64 arithmetic, multiply and
+// add rounded separately, then cast: bit-identical to the host generator.
+template <class Real>
+__global__ void __launch_bounds__(256)
+slab_spawn_kernel(uint64_t n_total, uint64_t seed_base, double radius, double width, double height, double vmin, double vmax,
+                  StepConst<Real> k, SlabGeom g, Rec<Real>* __restrict__ rec, uint32_t* __restrict__ pid, SlabDev* __restrict__ sd) {
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_total; i += stride) {
+        const double x = radius + (width - radius) * uniform01_dev(seed_base, i, 0);
+        const Real rx = (Real)x;
+        const Real fi = floor_r(div_rn(rx, k.grid_size));
+        const uint32_t gi = fi > (Real)0 ? (fi < (Real)g.gcols ? (uint32_t)fi : g.gcols - 1) : 0u;
+        if (gi < g.x0 || gi >= g.x1) continue;
+        const double y = radius + (height - radius) * uniform01_dev(seed_base, i, 1);
+        const double u = vmin + (vmax - vmin) * uniform01_dev(seed_base, i, 2);
+        const double w = vmin + (vmax - vmin) * uniform01_dev(seed_base, i, 3);
+        const uint32_t s = atomicAdd(&sd->own_e, 1u);
+        if (s >= g.cap) { atomicOr(&sd->err, SLAB_ERR_CAPACITY); continue; }
+        st_rec(rec + s, Rec<Real>{rx, (Real)y, (Real)u, (Real)w});
+        pid[s] = (uint32_t)i;
+    }
+}
+
+// ---- per sub-step kernels -----------------------------------------------------------------------
+template <class Real>
+__global__ void __launch_bounds__(256)
+slab_begin_kernel(SlabDev* __restrict__ sd, DevState* __restrict__ ds, void* send_l, void* send_r) {
+    if (threadIdx.x == 0 && blockIdx.x == 0) {
+        sd->n_own_prev = sd->own_e - sd->own_b;
+        sd->right_incomplete = 0;
+        ds->entries_used = 0;
+        reinterpret_cast<HaloHeader*>(send_l)->count = 0;
+        reinterpret_cast<HaloHeader*>(send_r)->count = 0;
+    }
+}
+
+// integrate + bounce, local cell + count for particles that stay in the local grid, migrants + halo into the send buffers
+template <class Real>
+__global__ void __launch_bounds__(256)
+slab_bin_kernel(const Rec<Real>* __restrict__ rec_old, const uint32_t* __restrict__ pid_old, StepConst<Real> k, SlabGeom g,
+                uint32_t* __restrict__ cell_count, uint32_t* __restrict__ slot_cell, uint32_t* __restrict__ arrival,
+                void* send_l, void* send_r, SlabDev* __restrict__ sd, DevState* __restrict__ ds) {
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= sd->n_own_prev) return;
+    const uint32_t s = sd->own_b + t;
+    Rec<Real> r = ld_rec(rec_old + s);
+    if (!ds->flags) integrate_rec<Real>(r, k);                      // error state: the state stays frozen
+    uint32_t gi, gj;
+    global_cell<Real>(r.x, r.y, k, g.gcols, gi, gj);
+    if (gi < g.xlo || gi >= g.xhi) atomicOr(&sd->err, SLAB_ERR_MIGRATION);
+    const uint32_t id = pid_old[s];
+    if (g.gl && gi <= g.x0) {                                        // migrant (gi < x0) or halo (gi == x0) for the left rank
+        const uint32_t j = atomicAdd(&reinterpret_cast<HaloHeader*>(send_l)->count, 1u);
+        if (j < g.cap_h) { st_rec(halo_recs<Real>(send_l) + j, r); halo_pids<Real>(send_l, g.cap_h)[j] = id; }
+        else atomicOr(&sd->err, SLAB_ERR_HALO);
+    }
+    if (g.gr && gi + 1 >= g.x1) {                                    // migrant (gi >= x1) or halo (gi == x1-1) for the right rank
+        const uint32_t j = atomicAdd(&reinterpret_cast<HaloHeader*>(send_r)->count, 1u);
+        if (j < g.cap_h) { st_rec(halo_recs<Real>(send_r) + j, r); halo_pids<Real>(send_r, g.cap_h)[j] = id; }
+        else atomicOr(&sd->err, SLAB_ERR_HALO);
+    }
+    if (gi >= g.col_off && gi < g.col_off + g.ncl) {                 // stays in the local grid (own or ghost column)
+        const uint32_t c = (gi - g.col_off) * g.rows + gj;
+        const uint32_t a = atomicAdd(cell_count + c, 1u);
+        slot_cell[t] = c; arrival[t] = a;
+        if (a >= 255u) atomicOr(&ds->flags, FLAG_CELL_OVERFLOW);
+    } else {
+        slot_cell[t] = SLAB_INVALID;
+    }
+}
+
+// received records (already integrated by their sender): input indices cap + j (left) and cap + cap_h + j (right)
+template <class Real>
+__global__ void __launch_bounds__(256)
+slab_bin_recv_kernel(void* recv_l, void* recv_r, StepConst<Real> k, SlabGeom g, uint32_t* __restrict__ cell_count,
+                     uint32_t* __restrict__ slot_cell, uint32_t* __restrict__ arrival, SlabDev* __restrict__ sd, DevState* __restrict__ ds) {
+    const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= 2 * g.cap_h) return;
+    const bool right = j >= g.cap_h;
+    if ((right && !g.gr) || (!right && !g.gl)) { slot_cell[g.cap + j] = SLAB_INVALID; return; }
+    void* buf = right ? recv_r : recv_l;
+    const uint32_t jj = right ? j - g.cap_h : j;
+    const uint32_t cnt = reinterpret_cast<const HaloHeader*>(buf)->count;
+    if (jj == 0 && cnt > g.cap_h) atomicOr(&sd->err, SLAB_ERR_HALO);
+    if (jj >= cnt || jj >= g.cap_h) { slot_cell[g.cap + j] = SLAB_INVALID; return; }
+    const Rec<Real> r = ld_rec(halo_recs<Real>(buf) + jj);
+    uint32_t gi, gj;
+    global_cell<Real>(r.x, r.y, k, g.gcols, gi, gj);
+    if (gi >= g.col_off && gi < g.col_off + g.ncl) {
+        const uint32_t c = (gi - g.col_off) * g.rows + gj;
+        const uint32_t a = atomicAdd(cell_count + c, 1u);
+        slot_cell[g.cap + j] = c; arrival[g.cap + j] = a;
+        if (a >= 255u) atomicOr(&ds->flags, FLAG_CELL_OVERFLOW);
+    } else {
+        slot_cell[g.cap + j] = SLAB_INVALID;                         // the neighbour's migrant deeper into its own slab: not ours to hold
+    }
+}
+
+__global__ void slab_counts_kernel(const uint32_t* __restrict__ cell_start, SlabGeom g, SlabDev* __restrict__ sd) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    const uint32_t rows = g.rows, ncl = g.ncl;
+    const uint32_t n = cell_start[ncl * rows];
+    sd->n_local = n;
+    if (n > g.cap) atomicOr(&sd->err, SLAB_ERR_CAPACITY);
+    sd->own_b = cell_start[g.gl * rows];
+    sd->own_e = cell_start[(ncl - g.gr) * rows];
+    sd->c_first1 = cell_start[ncl >= 1 ? rows : 0];
+    sd->c_first2 = cell_start[(ncl >= 2 ? 2 : ncl) * rows];
+    sd->c_last2 = cell_start[(ncl >= 2 ? ncl - 2 : 0) * rows];
+    sd->c_last1 = cell_start[(ncl >= 1 ? ncl - 1 : 0) * rows];
+    sd->n_blocked = g.gl ? sd->c_first2 : 0u;
+}
+
+template <class Real>
+__device__ __forceinline__ uint32_t slab_input_pid(uint32_t t, const uint32_t* pid_old, const SlabDev* sd, const SlabGeom& g, void* recv_l, void* recv_r) {
+    if (t < g.cap) return pid_old[sd->own_b + t];
+    const uint32_t j = t - g.cap;
+    return j < g.cap_h ? halo_pids<Real>(recv_l, g.cap_h)[j] : halo_pids<Real>(recv_r, g.cap_h)[j - g.cap_h];
+}
+
+template <class Real>
+__global__ void __launch_bounds__(256)
+slab_place_kernel(const uint32_t* __restrict__ slot_cell, const uint32_t* __restrict__ arrival, const uint32_t* __restrict__ pid_old,
+                  const uint32_t* __restrict__ cell_start, SlabGeom g, void* recv_l, void* recv_r,
+                  const SlabDev* __restrict__ sd, uint32_t* __restrict__ tmp_id) {
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= g.cap + 2 * g.cap_h || sd->err) return;
+    if (t < g.cap && t >= sd->n_own_prev) return;
+    const uint32_t c = slot_cell[t];
+    if (c == SLAB_INVALID) return;
+    const uint32_t dst = cell_start[c] + arrival[t];
+    if (dst < g.cap) tmp_id[dst] = slab_input_pid<Real>(t, pid_old, sd, g, recv_l, recv_r);
+}
+
+template <class Real>
+__global__ void __launch_bounds__(256)
+slab_move_kernel(const Rec<Real>* __restrict__ rec_old, const uint32_t* __restrict__ pid_old, const uint32_t* __restrict__ slot_cell,
+                 const uint32_t* __restrict__ cell_start, const uint32_t* __restrict__ tmp_id, StepConst<Real> k, SlabGeom g,
+                 void* recv_l, void* recv_r, const SlabDev* __restrict__ sd, const DevState* __restrict__ ds,
+                 Rec<Real>* __restrict__ rec_new, uint32_t* __restrict__ pid_new) {
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= g.cap + 2 * g.cap_h || sd->err) return;
+    if (t < g.cap && t >= sd->n_own_prev) return;
+    const uint32_t c = slot_cell[t];
+    if (c == SLAB_INVALID) return;
+    const uint32_t id = slab_input_pid<Real>(t, pid_old, sd, g, recv_l, recv_r);
+    const uint32_t b = cell_start[c], e = cell_start[c + 1];
+    uint32_t rank = 0;
+    for (uint32_t q = b; q < e; ++q) rank += tmp_id[q] < id ? 1u : 0u;       // ascending particle index inside the cell (:146-158)
+    Rec<Real> r;
+    if (t < g.cap) {
+        r = ld_rec(rec_old + sd->own_b + t);
+        if (!ds->flags) integrate_rec<Real>(r, k);                           // same arithmetic as slab_bin_kernel, bit for bit
+    } else {
+        const uint32_t j = t - g.cap;
+        r = j < g.cap_h ? ld_rec(halo_recs<Real>(recv_l) + j) : ld_rec(halo_recs<Real>(recv_r) + (j - g.cap_h));
+    }
+    st_rec(rec_new + b + rank, r);
+    pid_new[b + rank] = id;
+}
+
+// after phase A: do the particles of the last two local columns still have pending pairs?
+__global__ void __launch_bounds__(256)
+slab_right_check_kernel(const unsigned long long* __restrict__ head, const uint32_t* __restrict__ brem, SlabDev* __restrict__ sd) {
+    const uint32_t a = sd->c_last2 + blockIdx.x * blockDim.x + threadIdx.x;
+    if (a >= sd->n_local) return;
+    if (head_rem(head[a]) != 0u || brem[a] != 0u) sd->right_incomplete = 1u;
+}
+
+// M1 has been received into the records of the first two local columns: make their sub-lists visible
+__global__ void __launch_bounds__(256)
+slab_unblock_kernel(unsigned long long* __restrict__ head, uint32_t* __restrict__ brem, const uint32_t* __restrict__ entries,
+                    uint2* __restrict__ wl, uint32_t* __restrict__ wl_count, uint32_t r0, const SlabDev* __restrict__ sd) {
+    const uint32_t a = blockIdx.x * blockDim.x + threadIdx.x;
+    if (a >= sd->n_blocked) return;
+    const uint32_t rem = brem[a];
+    if (!rem) return;
+    brem[a] = 0u;
+    const uint32_t cur = head_cursor(head[a]);
+    head[a] = head_word(r0, rem, cur);                        // stamp r0 = "on the work list of round r0"
+    wl[atomicAdd(wl_count, 1u)] = make_uint2(a, entries[cur]);
+}
+
+// boundary hand-over (M1 / M2): a contiguous range of records with its length in front; fixed-size messages,
+// so that ranks that disagree about a count report SLAB_ERR_PROTOCOL instead of hanging inside NCCL
+template <class Real>
+__global__ void __launch_bounds__(256)
+slab_pack_kernel(const Rec<Real>* __restrict__ rec, const uint32_t* __restrict__ first_p, const uint32_t* __restrict__ last_p,
+                 uint32_t cap_h, void* buf, SlabDev* __restrict__ sd) {
+    const uint32_t first = *first_p, n = *last_p - first;
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        reinterpret_cast<HaloHeader*>(buf)->count = n;
+        if (n > cap_h) atomicOr(&sd->err, SLAB_ERR_HALO);
+    }
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n && i < cap_h) st_rec(halo_recs<Real>(buf) + i, ld_rec_cg(rec + first + i));
+}
+
+template <class Real>
+__global__ void __launch_bounds__(256)
+slab_unpack_kernel(void* buf, Rec<Real>* __restrict__ rec, const uint32_t* __restrict__ first_p, const uint32_t* __restrict__ last_p,
+                   uint32_t cap_h, SlabDev* __restrict__ sd) {
+    const uint32_t first = *first_p, n = *last_p - first;
+    const uint32_t got = reinterpret_cast<const HaloHeader*>(buf)->count;
+    if (got != n) { if (blockIdx.x == 0 && threadIdx.x == 0) atomicOr(&sd->err, SLAB_ERR_PROTOCOL); return; }
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n && i < cap_h) st_rec(rec + first + i, ld_rec(halo_recs<Real>(buf) + i));
+}
+
+template <class Real>
+__global__ void __launch_bounds__(256)
+slab_export_kernel(const Rec<Real>* __restrict__ rec, const uint32_t* __restrict__ pid, uint32_t first, uint32_t count,
+                   double2* __restrict__ pos, double2* __restrict__ vel, uint64_t* __restrict__ ids) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= count) return;
+    const Rec<Real> r = ld_rec(rec + first + i);
+    pos[i] = make_double2((double)r.x, (double)r.y);
+    vel[i] = make_double2((double)r.u, (double)r.w);
+    ids[i] = pid[first + i];
+}
+
+// ---- host side ------------------------------------------------------------------------------------
+template <class Real>
+struct SlabCollider {
+    ps_config cfg{};
+    int rank = 0, nranks = 1, device = 0;
+    uint64_t n_total = 0;
+    SlabGeom g{};
+    uint32_t ncell_local = 0;
+    NcclComm comm = nullptr;
+    bool t_acc = false;
+    uint64_t substeps_done = 0, launches = 0;
+    cudaStream_t own_stream = nullptr, stream = nullptr;
+    Error err;
+
+    int cur = 0;
+    Rec<Real>* rec[2] = {nullptr, nullptr};
+    uint32_t* pid[2] = {nullptr, nullptr};
+    uint32_t *cell_count = nullptr, *cell_start = nullptr, *scan_sums = nullptr;
+    uint32_t *slot_cell = nullptr, *arrival = nullptr, *tmp_id = nullptr, *brem = nullptr;
+    uint32_t* entries = nullptr; uint32_t entries_cap = 0;
+    unsigned long long* head = nullptr;
+    uint2* wl[3] = {nullptr, nullptr, nullptr};
+    void *send_l = nullptr, *send_r = nullptr, *recv_l = nullptr, *recv_r = nullptr;
+    DevState* ds = nullptr;
+    SlabDev* sd = nullptr;
+    struct HostCopy { SlabDev sd; DevState ds; };
+    HostCopy* hc = nullptr;          // pinned
+    SlabDev last{};                  // host copy after the most recent sub-step / load
+    int resolve_grid = 0;
+    void* stage = nullptr; size_t stage_bytes = 0;
+
+    int fail(int status, const std::string& text) { err.status = status; err.text = text; return status; }
+    int nccl_try(int rc, const char* what) {
+        if (rc == kNcclSuccess) return PS_OK;
+        const NcclApi& api = nccl_api();
+        return fail(PS_ERR_NCCL, std::string(what) + ": " + (api.GetErrorString ? api.GetErrorString(rc) : "NCCL error"));
+    }
+    template <class T> int alloc(T** p, uint64_t count) {
+        PS_CUDA_TRY(err, cudaMalloc((void**)p, (count ? count : 1) * sizeof(T)));
+        return PS_OK;
+    }
+
+    int create(const ps_config& c, int rank_, int nranks_, const NcclUniqueId* id, uint32_t rows, uint32_t cols) {
+        cfg = c; rank = rank_; nranks = nranks_; device = c.device; n_total = c.count;
+        PS_CUDA_TRY(err, cudaStreamCreateWithFlags(&own_stream, cudaStreamNonBlocking));
+        stream = own_stream;
+        g.rows = rows; g.gcols = cols;
+        g.x0 = (uint32_t)(((uint64_t)rank * cols) / nranks);
+        g.x1 = (uint32_t)(((uint64_t)(rank + 1) * cols) / nranks);
+        if (g.x1 - g.x0 < 2 && nranks > 1) return fail(PS_ERR_BAD_ARG, "ps_slab_create: every rank needs at least two cell columns");
+        g.gl = rank > 0 ? 1u : 0u; g.gr = rank < nranks - 1 ? 1u : 0u;
+        g.col_off = g.x0 - g.gl; g.ncl = (g.x1 - g.x0) + g.gl + g.gr;
+        g.xlo = rank > 0 ? (uint32_t)(((uint64_t)(rank - 1) * cols) / nranks) : 0u;
+        g.xhi = rank < nranks - 1 ? (uint32_t)(((uint64_t)(rank + 2) * cols) / nranks) : cols;
+        const uint64_t share = (n_total + nranks - 1) / nranks;
+        uint64_t cap = n_total <= (4u << 20) ? n_total : share + share / 4 + 16ull * rows + 4096;
+        if (cap > n_total) cap = n_total;
+        if (cap < 16) cap = 16;
+        g.cap = (uint32_t)cap;
+        g.cap_h = 4 * rows + 2048;
+        if (g.cap_h > g.cap) g.cap_h = g.cap;
+        ncell_local = g.ncl * rows;
+        const uint64_t per = c.contacts_per_particle ? c.contacts_per_particle : 12;
+        uint64_t ecap = per * cap; if (ecap > 0xfffffff0ull) ecap = 0xfffffff0ull;
+        entries_cap = (uint32_t)ecap;
+        int rc;
+        for (int i = 0; i < 2; ++i) { if ((rc = alloc(&rec[i], cap))) return rc; if ((rc = alloc(&pid[i], cap))) return rc; }
+        if ((rc = alloc(&cell_count, (uint64_t)ncell_local))) return rc;
+        if ((rc = alloc(&cell_start, (uint64_t)ncell_local + 3))) return rc;
+        if ((rc = alloc(&scan_sums, scan_tiles(ncell_local) + 1))) return rc;
+        const uint64_t nin = cap + 2ull * g.cap_h;
+        if ((rc = alloc(&slot_cell, nin))) return rc;
+        if ((rc = alloc(&arrival, nin))) return rc;
+        if ((rc = alloc(&tmp_id, cap))) return rc;
+        if ((rc = alloc(&brem, cap))) return rc;
+        if ((rc = alloc(&entries, (uint64_t)entries_cap))) return rc;
+        if ((rc = alloc(&head, cap))) return rc;
+        for (int i = 0; i < 3; ++i) if ((rc = alloc(&wl[i], cap))) return rc;
+        const size_t hb = halo_bytes<Real>(g.cap_h);
+        PS_CUDA_TRY(err, cudaMalloc(&send_l, hb)); PS_CUDA_TRY(err, cudaMalloc(&send_r, hb));
+        PS_CUDA_TRY(err, cudaMalloc(&recv_l, hb)); PS_CUDA_TRY(err, cudaMalloc(&recv_r, hb));
+        PS_CUDA_TRY(err, cudaMemsetAsync(send_l, 0, hb, stream)); PS_CUDA_TRY(err, cudaMemsetAsync(send_r, 0, hb, stream));
+        PS_CUDA_TRY(err, cudaMemsetAsync(recv_l, 0, hb, stream)); PS_CUDA_TRY(err, cudaMemsetAsync(recv_r, 0, hb, stream));
+        if ((rc = alloc(&ds, 1))) return rc;
+        if ((rc = alloc(&sd, 1))) return rc;
+        PS_CUDA_TRY(err, cudaMemsetAsync(ds, 0, sizeof(DevState), stream));
+        PS_CUDA_TRY(err, cudaMemsetAsync(sd, 0, sizeof(SlabDev), stream));
+        PS_CUDA_TRY(err, cudaMemsetAsync(brem, 0, cap * sizeof(uint32_t), stream));
+        PS_CUDA_TRY(err, cudaHostAlloc((void**)&hc, sizeof(HostCopy), cudaHostAllocDefault));
+        int per_sm = 0, sms = 0;
+        PS_CUDA_TRY(err, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, resolve_kernel<Real>, RESOLVE_THREADS, 0));
+        PS_CUDA_TRY(err, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+        resolve_grid = per_sm * sms;
+        if (nranks > 1) {
+            const NcclApi& api = nccl_api();
+            if (!api.ok) return fail(PS_ERR_NCCL, api.error);
+            if (!id) return fail(PS_ERR_BAD_ARG, "ps_slab_create: nccl id is NULL");
+            if ((rc = nccl_try(api.CommInitRank(&comm, nranks, *id, rank), "ncclCommInitRank"))) return rc;
+        }
+        PS_CUDA_TRY(err, cudaStreamSynchronize(stream));
+        return PS_OK;
+    }
+
+    void destroy() {
+        if (own_stream) cudaStreamSynchronize(own_stream);
+        if (comm) nccl_api().CommDestroy(comm);
+        for (auto& r : rec) cudaFree(r);
+        for (auto& p : pid) cudaFree(p);
+        for (auto& w : wl) cudaFree(w);
+        cudaFree(cell_count); cudaFree(cell_start); cudaFree(scan_sums); cudaFree(slot_cell); cudaFree(arrival);
+        cudaFree(tmp_id); cudaFree(brem); cudaFree(entries); cudaFree(head);
+        cudaFree(send_l); cudaFree(send_r); cudaFree(recv_l); cudaFree(recv_r); cudaFree(ds); cudaFree(sd); cudaFree(stage);
+        if (hc) cudaFreeHost(hc);
+        if (own_stream) cudaStreamDestroy(own_stream);
+    }
+
+    StepConst<Real> consts() const {
+        StepConst<Real> k = make_step_const<Real>(cfg, t_acc, g.rows, g.gcols);
+        k.cols = g.ncl;                 // the local grid is what the stencil walks; the global clamp uses g.gcols
+        return k;
+    }
+
+    int ensure_stage(size_t bytes) {
+        if (bytes <= stage_bytes) return PS_OK;
+        cudaFree(stage); stage = nullptr; stage_bytes = 0;
+        PS_CUDA_TRY(err, cudaMalloc(&stage, bytes));
+        stage_bytes = bytes;
+        return PS_OK;
+    }
+
+    int finish_load() {
+        PS_CUDA_TRY(err, cudaMemcpyAsync(&hc->sd, sd, sizeof(SlabDev), cudaMemcpyDeviceToHost, stream));
+        PS_CUDA_TRY(err, cudaStreamSynchronize(stream));
+        if (hc->sd.err & SLAB_ERR_CAPACITY) return fail(PS_ERR_CAPACITY, "this rank's slab holds more particles than it was sized for");
+        // slots [0, own_e) are all owned and in arbitrary order; the first sub-step sorts them
+        SlabDev h = hc->sd;
+        h.own_b = 0; h.n_local = h.own_e;
+        PS_CUDA_TRY(err, cudaMemcpyAsync(sd, &h, sizeof(SlabDev), cudaMemcpyHostToDevice, stream));
+        PS_CUDA_TRY(err, cudaStreamSynchronize(stream));
+        last = h;
+        return PS_OK;
+    }
+
+    int begin_load() {
+        PS_CUDA_TRY(err, cudaMemsetAsync(sd, 0, sizeof(SlabDev), stream));
+        PS_CUDA_TRY(err, cudaMemsetAsync(ds, 0, sizeof(DevState), stream));
+        cur = 0;
+        return PS_OK;
+    }
+
+    // every rank passes the same global arrays (n_total interleaved f64 pairs each) and keeps its own columns
+    int upload_global(const double* pos_xy, const double* vel_xy) {
+        int rc = begin_load(); if (rc) return rc;
+        const StepConst<Real> k = consts();
+        const uint64_t chunk = 4ull << 20;
+        rc = ensure_stage(2 * chunk * sizeof(double2)); if (rc) return rc;
+        double2* dpos = static_cast<double2*>(stage); double2* dvel = dpos + chunk;
+        for (uint64_t first = 0; first < n_total; first += chunk) {
+            const uint32_t m = (uint32_t)(n_total - first < chunk ? n_total - first : chunk);
+            PS_CUDA_TRY(err, cudaMemcpyAsync(dpos, pos_xy + 2 * first, m * sizeof(double2), cudaMemcpyHostToDevice, stream));
+            PS_CUDA_TRY(err, cudaMemcpyAsync(dvel, vel_xy + 2 * first, m * sizeof(double2), cudaMemcpyHostToDevice, stream));
+            slab_filter_kernel<Real><<<(m + 255) / 256, 256, 0, stream>>>(dpos, dvel, first, m, k, g, rec[cur], pid[cur], sd);
+            ++launches;
+            PS_CUDA_TRY(err, cudaStreamSynchronize(stream));    // pageable source: keep the staging buffer safe
+        }
+        return finish_load();
+    }
+
+    int spawn(uint64_t seed, double vmin, double vmax) {
+        int rc = begin_load(); if (rc) return rc;
+        const StepConst<Real> k = consts();
+        // splitmix64(seed) on the host = scenes.uniform01's `base`
+        uint64_t z = seed + 0x9E3779B97F4A7C15ull;
+        z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull; z = (z ^ (z >> 27)) * 0x94D049BB133111EBull; z ^= z >> 31;
+        slab_spawn_kernel<Real><<<148 * 16, 256, 0, stream>>>(n_total, z, cfg.radius, cfg.width, cfg.height, vmin, vmax, k, g, rec[cur], pid[cur], sd);
+        ++launches;
+        PS_CUDA_TRY(err, cudaGetLastError());
+        return finish_load();
+    }
+
+    int launch_resolve(const StepConst<Real>& k, uint32_t r0) {
+        Rec<Real>* a_rec = rec[cur ^ 1]; const uint32_t* a_ent = entries; unsigned long long* a_head = head;
+        uint2 *a0 = wl[0], *a1 = wl[1], *a2 = wl[2]; StepConst<Real> a_k = k; DevState* a_ds = ds; uint32_t a_r0 = r0;
+        void* args[] = {&a_rec, &a_ent, &a_head, &a0, &a1, &a2, &a_k, &a_ds, &a_r0};
+        const uint64_t want = ((uint64_t)g.cap + RESOLVE_THREADS - 1) / RESOLVE_THREADS;
+        const unsigned grid = (unsigned)(want < (uint64_t)resolve_grid ? want : (uint64_t)resolve_grid);
+        PS_CUDA_TRY(err, cudaLaunchCooperativeKernel((const void*)resolve_kernel<Real>, dim3(grid), dim3(RESOLVE_THREADS), args, 0, stream));
+        ++launches;
+        return PS_OK;
+    }
+
+    int read_back() {
+        PS_CUDA_TRY(err, cudaMemcpyAsync(&hc->sd, sd, sizeof(SlabDev), cudaMemcpyDeviceToHost, stream));
+        PS_CUDA_TRY(err, cudaMemcpyAsync(&hc->ds, ds, sizeof(DevState), cudaMemcpyDeviceToHost, stream));
+        PS_CUDA_TRY(err, cudaStreamSynchronize(stream));
+        const uint32_t e = hc->sd.err;
+        if (e & SLAB_ERR_MIGRATION) return fail(PS_ERR_MIGRATION, "a particle crossed a whole neighbouring slab in one sub-step");
+        if (e & SLAB_ERR_HALO) return fail(PS_ERR_CAPACITY, "halo / migration buffer too small for this scene");
+        if (e & SLAB_ERR_CAPACITY) return fail(PS_ERR_CAPACITY, "this rank's slab holds more particles than it was sized for");
+        if (hc->ds.flags & FLAG_CAPACITY) return fail(PS_ERR_CAPACITY, "contact list exceeded its capacity; raise ps_config.contacts_per_particle");
+        if (hc->ds.flags & FLAG_CELL_OVERFLOW) return fail(PS_ERR_CELL_OVERFLOW, "a grid cell held more than 255 particles (src/core.zig:51,132)");
+        return PS_OK;
+    }
+
+    // One iteration of the loop body at src/core.zig:247-267, this rank's share.
+    int substep() {
+        if (err.status != PS_OK) return err.status;
+        const NcclApi& api = nccl_api();
+        const StepConst<Real> k = consts();
+        const int nw = cur ^ 1;
+        const size_t hb = halo_bytes<Real>(g.cap_h);
+        const unsigned g_cap = (g.cap + 255) / 256, g_in = (g.cap + 2 * g.cap_h + 255) / 256, g_h = (2 * g.cap_h + 255) / 256;
+        cudaStream_t st = stream;
+        int rc;
+        PS_CUDA_TRY(err, cudaMemsetAsync(cell_count, 0, (size_t)ncell_local * sizeof(uint32_t), st));
+        slab_begin_kernel<Real><<<1, 32, 0, st>>>(sd, ds, send_l, send_r);
+        slab_bin_kernel<Real><<<g_cap, 256, 0, st>>>(rec[cur], pid[cur], k, g, cell_count, slot_cell, arrival, send_l, send_r, sd, ds);
+        launches += 2;
+        if (nranks > 1) {                                                         // ---- M0: migrants + halo, both ways
+            if ((rc = nccl_try(api.GroupStart(), "ncclGroupStart"))) return rc;
+            if (g.gl) { api.Send(send_l, hb, kNcclUint8, rank - 1, comm, st); api.Recv(recv_l, hb, kNcclUint8, rank - 1, comm, st); }
+            if (g.gr) { api.Send(send_r, hb, kNcclUint8, rank + 1, comm, st); api.Recv(recv_r, hb, kNcclUint8, rank + 1, comm, st); }
+            if ((rc = nccl_try(api.GroupEnd(), "ncclGroupEnd (M0)"))) return rc;
+        }
+        slab_bin_recv_kernel<Real><<<g_h, 256, 0, st>>>(recv_l, recv_r, k, g, cell_count, slot_cell, arrival, sd, ds);
+        PS_CUDA_TRY(err, exclusive_scan_u32(cell_count, cell_start, ncell_local, scan_sums, cell_start + ncell_local, &ds->max_cell, st));
+        slab_counts_kernel<<<1, 32, 0, st>>>(cell_start, g, sd);
+        slab_place_kernel<Real><<<g_in, 256, 0, st>>>(slot_cell, arrival, pid[cur], cell_start, g, recv_l, recv_r, sd, tmp_id);
+        slab_move_kernel<Real><<<g_in, 256, 0, st>>>(rec[cur], pid[cur], slot_cell, cell_start, tmp_id, k, g, recv_l, recv_r, sd, ds, rec[nw], pid[nw]);
+        SlabView sv{g.gl, g.gr, g.ncl, g.col_off, g.gcols, &sd->n_local, &sd->n_blocked, brem};
+        detect_kernel<Real, true><<<g_cap, 256, 0, st>>>(rec[nw], cell_start, 0u, k, entries, entries_cap, head, wl[0], ds, sv);
+        launches += 9;
+        if ((rc = launch_resolve(k, 0u))) return rc;                              // ---- phase A
+        if (g.gr) { slab_right_check_kernel<<<g_cap, 256, 0, st>>>(head, brem, sd); ++launches; }
+        if ((rc = read_back())) return rc;                                        // the one host synchronisation of the sub-step
+        const SlabDev h = hc->sd;
+        const uint32_t r0 = hc->ds.rounds_last + 1;
+        const unsigned g_hh = (g.cap_h + 255) / 256;
+        const bool send_now = g.gr && !h.right_incomplete;
+        // ---- M1: the states of the last own column + right ghost column go to the right rank, whose left ghost
+        //      column + first own column they are (same particles, same order)
+        if (send_now) { slab_pack_kernel<Real><<<g_hh, 256, 0, st>>>(rec[nw], &sd->c_last2, &sd->n_local, g.cap_h, send_r, sd); ++launches; }
+        if (nranks > 1) {
+            if ((rc = nccl_try(api.GroupStart(), "ncclGroupStart"))) return rc;
+            if (send_now) api.Send(send_r, hb, kNcclUint8, rank + 1, comm, st);
+            if (g.gl) api.Recv(recv_l, hb, kNcclUint8, rank - 1, comm, st);
+            if ((rc = nccl_try(api.GroupEnd(), "ncclGroupEnd (M1)"))) return rc;
+        }
+        if (g.gl) {                                                               // ---- phase B
+            slab_unpack_kernel<Real><<<g_hh, 256, 0, st>>>(recv_l, rec[nw], &sd->zero, &sd->c_first2, g.cap_h, sd);
+            slab_unblock_kernel<<<(h.c_first2 + 255) / 256 + 1, 256, 0, st>>>(head, brem, entries, wl[r0 % 3], &ds->wl_count[r0 % 3], r0, sd);
+            launches += 2;
+            if ((rc = launch_resolve(k, r0))) return rc;
+        }
+        if (g.gr && !send_now) {                                                  // rare: our right boundary depended on the left one
+            slab_pack_kernel<Real><<<g_hh, 256, 0, st>>>(rec[nw], &sd->c_last2, &sd->n_local, g.cap_h, send_r, sd); ++launches;
+            if ((rc = nccl_try(api.Send(send_r, hb, kNcclUint8, rank + 1, comm, st), "ncclSend (late M1)"))) return rc;
+        }
+        // ---- M2: the left ghost column's final states return to the left rank (its last own column)
+        if (g.gl) { slab_pack_kernel<Real><<<g_hh, 256, 0, st>>>(rec[nw], &sd->zero, &sd->c_first1, g.cap_h, send_l, sd); ++launches; }
+        if (nranks > 1) {
+            if ((rc = nccl_try(api.GroupStart(), "ncclGroupStart"))) return rc;
+            if (g.gl) api.Send(send_l, hb, kNcclUint8, rank - 1, comm, st);
+            if (g.gr) api.Recv(recv_r, hb, kNcclUint8, rank + 1, comm, st);
+            if ((rc = nccl_try(api.GroupEnd(), "ncclGroupEnd (M2)"))) return rc;
+        }
+        if (g.gr) { slab_unpack_kernel<Real><<<g_hh, 256, 0, st>>>(recv_r, rec[nw], &sd->c_last2, &sd->c_last1, g.cap_h, sd); ++launches; }
+        PS_CUDA_TRY(err, cudaGetLastError());
+        cur = nw;
+        last = h;
+        ++substeps_done;
+        return PS_OK;
+    }
+
+    int sync() {
+        if (err.status != PS_OK) return err.status;
+        PS_CUDA_TRY(err, cudaMemcpyAsync(&hc->sd, sd, sizeof(SlabDev), cudaMemcpyDeviceToHost, stream));
+        PS_CUDA_TRY(err, cudaStreamSynchronize(stream));
+        if (hc->sd.err & SLAB_ERR_PROTOCOL) return fail(PS_ERR_NCCL, "boundary hand-over sizes disagree between neighbouring ranks");
+        if (hc->sd.err & SLAB_ERR_HALO) return fail(PS_ERR_CAPACITY, "halo / migration buffer too small for this scene");
+        return PS_OK;
+    }
+
+    // this rank's owned particles: global indices + interleaved f64 position / velocity
+    int download_owned(uint64_t* ids, double* pos_xy, double* vel_xy, uint64_t cap_out, uint64_t* count) {
+        PS_CUDA_TRY(err, cudaStreamSynchronize(stream));
+        const uint32_t n = last.own_e - last.own_b;
+        *count = n;
+        if (n == 0) return PS_OK;
+        if (cap_out < n) return fail(PS_ERR_BAD_ARG, "ps_slab_download_owned: output arrays too small");
+        int rc = ensure_stage((size_t)n * (2 * sizeof(double2) + sizeof(uint64_t))); if (rc) return rc;
+        double2* dpos = static_cast<double2*>(stage); double2* dvel = dpos + n; uint64_t* dids = reinterpret_cast<uint64_t*>(dvel + n);
+        slab_export_kernel<Real><<<(n + 255) / 256, 256, 0, stream>>>(rec[cur], pid[cur], last.own_b, n, dpos, dvel, dids);
+        ++launches;
+        if (pos_xy) PS_CUDA_TRY(err, cudaMemcpyAsync(pos_xy, dpos, (size_t)n * sizeof(double2), cudaMemcpyDeviceToHost, stream));
+        if (vel_xy) PS_CUDA_TRY(err, cudaMemcpyAsync(vel_xy, dvel, (size_t)n * sizeof(double2), cudaMemcpyDeviceToHost, stream));
+        if (ids) PS_CUDA_TRY(err, cudaMemcpyAsync(ids, dids, (size_t)n * sizeof(uint64_t), cudaMemcpyDeviceToHost, stream));
+        PS_CUDA_TRY(err, cudaStreamSynchronize(stream));
+        return PS_OK;
+    }
+
+    int stats(ps_stats* out) {
+        PS_CUDA_TRY(err, cudaMemcpyAsync(&hc->ds, ds, sizeof(DevState), cudaMemcpyDeviceToHost, stream));
+        PS_CUDA_TRY(err, cudaStreamSynchronize(stream));
+        std::memset(out, 0, sizeof(*out));
+        out->substeps_done = substeps_done;
+        out->pairs_last = hc->ds.inc_total / 2;
+        out->pairs_total = hc->ds.pairs_total;
+        out->rounds_last = hc->ds.rounds_last;
+        out->rounds_total = hc->ds.rounds_total;
+        out->max_cell_count = hc->ds.max_cell;
+        out->kernel_launches = launches;
+        return PS_OK;
+    }
+};
+
+}  // namespace ps
