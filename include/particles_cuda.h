@@ -212,6 +212,20 @@ int ps_slab_download_owned(ps_slab* slab, uint64_t* ids, double* pos_xy, double*
 int ps_slab_get_stats(ps_slab* slab, ps_stats* out);           /* pairs_* count the pairs whose centre this rank owns */
 const char* ps_slab_last_error(const ps_slab* slab);
 
+/* The same slab decomposition with all ranks emulated in ONE process on ONE GPU (device copies where the
+ * multi-process path has NCCL messages).  Same kernels, same protocol, same results; it exists so that the
+ * multi-rank path can be tested and profiled on a single-GPU box.  No counterpart in the reference. */
+typedef struct ps_slabgroup ps_slabgroup;
+int ps_slabgroup_create(const ps_config* cfg, int nranks, ps_slabgroup** out);
+void ps_slabgroup_destroy(ps_slabgroup* grp);
+int ps_slabgroup_upload_global(ps_slabgroup* grp, const double* pos_xy, const double* vel_xy);
+int ps_slabgroup_set_acc(ps_slabgroup* grp, int on);
+int ps_slabgroup_step_substeps(ps_slabgroup* grp, uint64_t substeps);
+int ps_slabgroup_owned_count(ps_slabgroup* grp, int rank, uint64_t* count);
+int ps_slabgroup_download_owned(ps_slabgroup* grp, int rank, uint64_t* ids, double* pos_xy, double* vel_xy, uint64_t cap, uint64_t* count);
+int ps_slabgroup_get_stats(ps_slabgroup* grp, int rank, ps_stats* out);
+const char* ps_slabgroup_last_error(const ps_slabgroup* grp);
+
 #ifdef __cplusplus
 }
 #endif

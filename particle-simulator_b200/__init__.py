@@ -7,6 +7,6 @@ The directory name carries a hyphen; ``import particle_simulator_b200`` (the ali
 the repository root) loads it.
 """
 from . import build, capi, core, scenes  # noqa: F401
-from .core import Particles, Simulation, SlabSimulation, Solver, SpatialHashGrid, Spawner  # noqa: F401
+from .core import Particles, Simulation, SlabGroup, SlabSimulation, Solver, SpatialHashGrid, Spawner  # noqa: F401
 
-__all__ = ["build", "capi", "core", "scenes", "Particles", "Simulation", "SlabSimulation", "Solver", "SpatialHashGrid", "Spawner"]
+__all__ = ["build", "capi", "core", "scenes", "Particles", "Simulation", "SlabGroup", "SlabSimulation", "Solver", "SpatialHashGrid", "Spawner"]

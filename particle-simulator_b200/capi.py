@@ -115,6 +115,15 @@ SYMBOLS = {
     "ps_slab_download_owned": (ctypes.c_int, [_P, _P, _P, _P, _U64, _PU64]),
     "ps_slab_get_stats": (ctypes.c_int, [_P, ctypes.POINTER(PsStats)]),
     "ps_slab_last_error": (ctypes.c_char_p, [_P]),
+    "ps_slabgroup_create": (ctypes.c_int, [_CFG, ctypes.c_int, _PP]),
+    "ps_slabgroup_destroy": (None, [_P]),
+    "ps_slabgroup_upload_global": (ctypes.c_int, [_P, _P, _P]),
+    "ps_slabgroup_set_acc": (ctypes.c_int, [_P, ctypes.c_int]),
+    "ps_slabgroup_step_substeps": (ctypes.c_int, [_P, _U64]),
+    "ps_slabgroup_owned_count": (ctypes.c_int, [_P, ctypes.c_int, _PU64]),
+    "ps_slabgroup_download_owned": (ctypes.c_int, [_P, ctypes.c_int, _P, _P, _P, _U64, _PU64]),
+    "ps_slabgroup_get_stats": (ctypes.c_int, [_P, ctypes.c_int, ctypes.POINTER(PsStats)]),
+    "ps_slabgroup_last_error": (ctypes.c_char_p, [_P]),
 }
 
 # not part of the stable ABI (tuning hooks used by bench.py --sweep)

@@ -437,3 +437,68 @@ class SlabSimulation:
         s = capi.PsStats()
         self._check(self._L.ps_slab_get_stats(self._h, ctypes.byref(s)))
         return {k: int(getattr(s, k)) for k, _ in capi.PsStats._fields_ if k != "reserved"}
+
+
+class SlabGroup:
+    """All ranks of a slab-decomposed scene emulated in one process on one GPU (ps_slabgroup_*): the multi-rank
+    protocol with device copies instead of NCCL.  For tests and for boxes with fewer GPUs than slabs."""
+
+    def __init__(self, scene: scenes.Scene, nranks: int, *, precision: str = "f64", device: int = 0, contacts_per_particle: int = 0):
+        self._L = capi.load()
+        cfg = capi.PsConfig()
+        cfg.struct_size = ctypes.sizeof(capi.PsConfig)
+        cfg.device = device
+        cfg.count = scene.count
+        cfg.radius, cfg.width, cfg.height, cfg.grid_size = scene.radius, scene.width, scene.height, scene.grid_size
+        cfg.target_fps, cfg.sub_steps, cfg.g = scene.target_fps, scene.sub_steps, scene.g
+        cfg.boundary_damping, cfg.particle_damping = scene.boundary_damping, scene.particle_damping
+        cfg.precision = capi.PS_F64 if precision == "f64" else capi.PS_F32
+        cfg.collisions = 1
+        cfg.contacts_per_particle = contacts_per_particle
+        self.scene, self.nranks = scene, nranks
+        h = ctypes.c_void_p()
+        rc = self._L.ps_slabgroup_create(ctypes.byref(cfg), nranks, ctypes.byref(h))
+        if rc != capi.PS_OK:
+            raise capi.PsError(rc, (self._L.ps_slabgroup_last_error(None) or b"").decode())
+        self._h = h
+
+    def _check(self, rc):
+        if rc != capi.PS_OK:
+            raise capi.PsError(rc, (self._L.ps_slabgroup_last_error(self._h) or self._L.ps_status_string(rc) or b"").decode())
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.ps_slabgroup_destroy(self._h)
+            self._h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def upload_global(self, pos, vel):
+        assert pos.dtype == np.float64 and pos.flags.c_contiguous and vel.flags.c_contiguous
+        self._check(self._L.ps_slabgroup_upload_global(self._h, ctypes.c_void_p(pos.ctypes.data), ctypes.c_void_p(vel.ctypes.data)))
+
+    def set_acc(self, on):
+        self._check(self._L.ps_slabgroup_set_acc(self._h, int(on)))
+
+    def step_substeps(self, n):
+        self._check(self._L.ps_slabgroup_step_substeps(self._h, n))
+
+    def download_owned(self, rank):
+        n = ctypes.c_uint64()
+        self._check(self._L.ps_slabgroup_owned_count(self._h, rank, ctypes.byref(n)))
+        m = max(int(n.value), 1)
+        ids = np.empty(m, dtype=np.uint64); pos = np.empty((m, 2)); vel = np.empty((m, 2))
+        cnt = ctypes.c_uint64()
+        self._check(self._L.ps_slabgroup_download_owned(self._h, rank, ctypes.c_void_p(ids.ctypes.data), ctypes.c_void_p(pos.ctypes.data),
+                                                        ctypes.c_void_p(vel.ctypes.data), m, ctypes.byref(cnt)))
+        m = int(cnt.value)
+        return ids[:m], pos[:m], vel[:m]
+
+    def stats(self, rank):
+        s = capi.PsStats()
+        self._check(self._L.ps_slabgroup_get_stats(self._h, rank, ctypes.byref(s)))
+        return {k: int(getattr(s, k)) for k, _ in capi.PsStats._fields_ if k != "reserved"}

@@ -543,6 +543,94 @@ int ps_slab_download_owned(ps_slab* s, uint64_t* ids, double* pos, double* vel, 
 int ps_slab_get_stats(ps_slab* s, ps_stats* out) { return (s && out) ? s->stats(out) : PS_ERR_BAD_ARG; }
 const char* ps_slab_last_error(const ps_slab* s) { return s ? s->last_error() : g_create_error.c_str(); }
 
+// ---- several slab ranks emulated in one process ---------------------------------------------------------------
+}  // extern "C"
+
+struct ps_slabgroup {
+    virtual ~ps_slabgroup() {}
+    virtual int upload_global(const double* pos, const double* vel) = 0;
+    virtual int set_acc(bool on) = 0;
+    virtual int step(uint64_t substeps) = 0;
+    virtual int owned_count(int rank, uint64_t* n) = 0;
+    virtual int download_owned(int rank, uint64_t* ids, double* pos, double* vel, uint64_t cap, uint64_t* count) = 0;
+    virtual int stats(int rank, ps_stats* out) = 0;
+    virtual const char* last_error() const = 0;
+};
+
+namespace {
+template <class Real>
+struct SlabGroupT final : ps_slabgroup {
+    ps::SlabGroupLocal<Real> grp;
+    int device = 0;
+    std::string text;
+    int note(int rc, const ps::Error& e) { if (rc != PS_OK) text = e.text; return rc; }
+    bool bad(int rank) const { return rank < 0 || rank >= (int)grp.ranks.size(); }
+    int upload_global(const double* pos, const double* vel) override {
+        DeviceGuard g(device);
+        for (auto* r : grp.ranks) { const int rc = r->upload_global(pos, vel); if (rc != PS_OK) return note(rc, r->err); }
+        return PS_OK;
+    }
+    int set_acc(bool on) override { for (auto* r : grp.ranks) r->t_acc = on; return PS_OK; }
+    int step(uint64_t substeps) override {
+        DeviceGuard g(device);
+        for (uint64_t s = 0; s < substeps; ++s) { const int rc = grp.substep(); if (rc != PS_OK) return note(rc, grp.err); }
+        for (auto* r : grp.ranks) { const int rc = r->sync(); if (rc != PS_OK) return note(rc, r->err); }
+        return PS_OK;
+    }
+    int owned_count(int rank, uint64_t* n) override { if (bad(rank)) return PS_ERR_BAD_ARG; *n = grp.ranks[rank]->last.own_e - grp.ranks[rank]->last.own_b; return PS_OK; }
+    int download_owned(int rank, uint64_t* ids, double* pos, double* vel, uint64_t cap, uint64_t* count) override {
+        if (bad(rank)) return PS_ERR_BAD_ARG;
+        DeviceGuard g(device);
+        return note(grp.ranks[rank]->download_owned(ids, pos, vel, cap, count), grp.ranks[rank]->err);
+    }
+    int stats(int rank, ps_stats* out) override {
+        if (bad(rank)) return PS_ERR_BAD_ARG;
+        DeviceGuard g(device);
+        return note(grp.ranks[rank]->stats(out), grp.ranks[rank]->err);
+    }
+    const char* last_error() const override { return text.c_str(); }
+};
+
+template <class Real>
+int slabgroup_create_t(const ps_config* cfg, int nranks, uint32_t rows, uint32_t cols, ps_slabgroup** out) {
+    auto* s = new (std::nothrow) SlabGroupT<Real>();
+    if (!s) { g_create_error = "host allocation failed"; return PS_ERR_OOM; }
+    s->device = cfg->device;
+    DeviceGuard g(cfg->device);
+    const int rc = s->grp.create(*cfg, nranks, rows, cols);
+    if (rc != PS_OK) { g_create_error = s->grp.err.text; delete s; return rc; }
+    *out = s;
+    return PS_OK;
+}
+}  // namespace
+
+extern "C" {
+
+int ps_slabgroup_create(const ps_config* cfg, int nranks, ps_slabgroup** out) {
+    if (!out) { g_create_error = "out is NULL"; return PS_ERR_BAD_ARG; }
+    *out = nullptr;
+    uint32_t rows = 0, cols = 0;
+    std::string why;
+    int rc = validate(cfg, &rows, &cols, &why);
+    if (rc != PS_OK) { g_create_error = "ps_slabgroup_create: " + why; return rc; }
+    if (!cfg->collisions || nranks < 1 || cfg->count >= (1ull << 32)) { g_create_error = "ps_slabgroup_create: bad arguments"; return PS_ERR_BAD_ARG; }
+    int ndev = 0;
+    const cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) { cudaGetLastError(); g_create_error = "ps_slabgroup_create: no CUDA device; this library has no CPU path"; return PS_ERR_NO_DEVICE; }
+    if (cfg->device < 0 || cfg->device >= ndev) { g_create_error = "ps_slabgroup_create: device ordinal out of range"; return PS_ERR_BAD_ARG; }
+    return cfg->precision == PS_F64 ? slabgroup_create_t<double>(cfg, nranks, rows, cols, out) : slabgroup_create_t<float>(cfg, nranks, rows, cols, out);
+}
+void ps_slabgroup_destroy(ps_slabgroup* g) { delete g; }
+int ps_slabgroup_upload_global(ps_slabgroup* g, const double* pos, const double* vel) { return (g && pos && vel) ? g->upload_global(pos, vel) : PS_ERR_BAD_ARG; }
+int ps_slabgroup_set_acc(ps_slabgroup* g, int on) { return g ? g->set_acc(on != 0) : PS_ERR_BAD_ARG; }
+int ps_slabgroup_step_substeps(ps_slabgroup* g, uint64_t substeps) { return g ? g->step(substeps) : PS_ERR_BAD_ARG; }
+int ps_slabgroup_owned_count(ps_slabgroup* g, int rank, uint64_t* n) { return (g && n) ? g->owned_count(rank, n) : PS_ERR_BAD_ARG; }
+int ps_slabgroup_download_owned(ps_slabgroup* g, int rank, uint64_t* ids, double* pos, double* vel, uint64_t cap, uint64_t* count) {
+    return (g && count) ? g->download_owned(rank, ids, pos, vel, cap, count) : PS_ERR_BAD_ARG;
+}
+int ps_slabgroup_get_stats(ps_slabgroup* g, int rank, ps_stats* out) { return (g && out) ? g->stats(rank, out) : PS_ERR_BAD_ARG; }
+const char* ps_slabgroup_last_error(const ps_slabgroup* g) { return g ? g->last_error() : g_create_error.c_str(); }
+
 // ---- ps_compute_start_array_static: the same prefix sum with no allocation anywhere ------------------
 //
 // Scratch for the per-tile partial sums lives in the file-scope device array below instead of memory

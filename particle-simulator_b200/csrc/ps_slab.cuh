@@ -415,10 +415,9 @@ struct SlabCollider {
         PS_CUDA_TRY(err, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, resolve_kernel<Real>, RESOLVE_THREADS, 0));
         PS_CUDA_TRY(err, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
         resolve_grid = per_sm * sms;
-        if (nranks > 1) {
+        if (nranks > 1 && id) {                // id == NULL: ranks emulated in one process (SlabGroupLocal), no communicator
             const NcclApi& api = nccl_api();
             if (!api.ok) return fail(PS_ERR_NCCL, api.error);
-            if (!id) return fail(PS_ERR_BAD_ARG, "ps_slab_create: nccl id is NULL");
             if ((rc = nccl_try(api.CommInitRank(&comm, nranks, *id, rank), "ncclCommInitRank"))) return rc;
         }
         PS_CUDA_TRY(err, cudaStreamSynchronize(stream));
@@ -526,26 +525,34 @@ struct SlabCollider {
         return PS_OK;
     }
 
-    // One iteration of the loop body at src/core.zig:247-267, this rank's share.
-    int substep() {
+    // ---- one sub-step (the loop body at src/core.zig:247-267, this rank's share) in stages ------------------
+    // The stages are separate so that the same code runs with NCCL between processes (substep()) or with plain
+    // device copies between several ranks emulated in one process on one GPU (SlabGroupLocal, used by the tests).
+    StepConst<Real> k_step{};
+    SlabDev h_step{};
+    uint32_t r0_step = 0;
+    bool send_now_step = false;
+    size_t halo_msg_bytes() const { return halo_bytes<Real>(g.cap_h); }
+
+    // stage 1: integrate + bin own particles; send_l / send_r now hold the M0 messages
+    int stage_bin() {
         if (err.status != PS_OK) return err.status;
-        const NcclApi& api = nccl_api();
-        const StepConst<Real> k = consts();
-        const int nw = cur ^ 1;
-        const size_t hb = halo_bytes<Real>(g.cap_h);
-        const unsigned g_cap = (g.cap + 255) / 256, g_in = (g.cap + 2 * g.cap_h + 255) / 256, g_h = (2 * g.cap_h + 255) / 256;
+        k_step = consts();
         cudaStream_t st = stream;
-        int rc;
         PS_CUDA_TRY(err, cudaMemsetAsync(cell_count, 0, (size_t)ncell_local * sizeof(uint32_t), st));
         slab_begin_kernel<Real><<<1, 32, 0, st>>>(sd, ds, send_l, send_r);
-        slab_bin_kernel<Real><<<g_cap, 256, 0, st>>>(rec[cur], pid[cur], k, g, cell_count, slot_cell, arrival, send_l, send_r, sd, ds);
+        slab_bin_kernel<Real><<<(g.cap + 255) / 256, 256, 0, st>>>(rec[cur], pid[cur], k_step, g, cell_count, slot_cell, arrival, send_l, send_r, sd, ds);
         launches += 2;
-        if (nranks > 1) {                                                         // ---- M0: migrants + halo, both ways
-            if ((rc = nccl_try(api.GroupStart(), "ncclGroupStart"))) return rc;
-            if (g.gl) { api.Send(send_l, hb, kNcclUint8, rank - 1, comm, st); api.Recv(recv_l, hb, kNcclUint8, rank - 1, comm, st); }
-            if (g.gr) { api.Send(send_r, hb, kNcclUint8, rank + 1, comm, st); api.Recv(recv_r, hb, kNcclUint8, rank + 1, comm, st); }
-            if ((rc = nccl_try(api.GroupEnd(), "ncclGroupEnd (M0)"))) return rc;
-        }
+        PS_CUDA_TRY(err, cudaGetLastError());
+        return PS_OK;
+    }
+
+    // stage 2 (recv_l / recv_r hold the neighbours' M0): local sort, detect, phase A, one host synchronisation
+    int stage_build() {
+        const int nw = cur ^ 1;
+        const unsigned g_cap = (g.cap + 255) / 256, g_in = (g.cap + 2 * g.cap_h + 255) / 256, g_h = (2 * g.cap_h + 255) / 256;
+        cudaStream_t st = stream;
+        const StepConst<Real>& k = k_step;
         slab_bin_recv_kernel<Real><<<g_h, 256, 0, st>>>(recv_l, recv_r, k, g, cell_count, slot_cell, arrival, sd, ds);
         PS_CUDA_TRY(err, exclusive_scan_u32(cell_count, cell_start, ncell_local, scan_sums, cell_start + ncell_local, &ds->max_cell, st));
         slab_counts_kernel<<<1, 32, 0, st>>>(cell_start, g, sd);
@@ -554,47 +561,91 @@ struct SlabCollider {
         SlabView sv{g.gl, g.gr, g.ncl, g.col_off, g.gcols, &sd->n_local, &sd->n_blocked, brem};
         detect_kernel<Real, true><<<g_cap, 256, 0, st>>>(rec[nw], cell_start, 0u, k, entries, entries_cap, head, wl[0], ds, sv);
         launches += 9;
-        if ((rc = launch_resolve(k, 0u))) return rc;                              // ---- phase A
+        int rc;
+        if ((rc = launch_resolve(k, 0u))) return rc;                              // phase A
         if (g.gr) { slab_right_check_kernel<<<g_cap, 256, 0, st>>>(head, brem, sd); ++launches; }
         if ((rc = read_back())) return rc;                                        // the one host synchronisation of the sub-step
-        const SlabDev h = hc->sd;
-        const uint32_t r0 = hc->ds.rounds_last + 1;
-        const unsigned g_hh = (g.cap_h + 255) / 256;
-        const bool send_now = g.gr && !h.right_incomplete;
-        // ---- M1: the states of the last own column + right ghost column go to the right rank, whose left ghost
-        //      column + first own column they are (same particles, same order)
-        if (send_now) { slab_pack_kernel<Real><<<g_hh, 256, 0, st>>>(rec[nw], &sd->c_last2, &sd->n_local, g.cap_h, send_r, sd); ++launches; }
-        if (nranks > 1) {
+        h_step = hc->sd;
+        r0_step = hc->ds.rounds_last + 1;
+        send_now_step = g.gr && !h_step.right_incomplete;
+        return PS_OK;
+    }
+
+    // M1 out: last own column + right ghost column -> send_r (they are the right rank's left ghost + first own column)
+    int pack_m1() {
+        slab_pack_kernel<Real><<<(g.cap_h + 255) / 256, 256, 0, stream>>>(rec[cur ^ 1], &sd->c_last2, &sd->n_local, g.cap_h, send_r, sd);
+        ++launches;
+        PS_CUDA_TRY(err, cudaGetLastError());
+        return PS_OK;
+    }
+
+    // stage 3 (recv_l holds the left rank's M1): take over the boundary states, unblock, phase B
+    int stage_phase_b() {
+        cudaStream_t st = stream;
+        slab_unpack_kernel<Real><<<(g.cap_h + 255) / 256, 256, 0, st>>>(recv_l, rec[cur ^ 1], &sd->zero, &sd->c_first2, g.cap_h, sd);
+        slab_unblock_kernel<<<(h_step.c_first2 + 255) / 256 + 1, 256, 0, st>>>(head, brem, entries, wl[r0_step % 3], &ds->wl_count[r0_step % 3], r0_step, sd);
+        launches += 2;
+        return launch_resolve(k_step, r0_step);
+    }
+
+    // M2 out: the left ghost column's final states -> send_l (the left rank's last own column)
+    int pack_m2() {
+        slab_pack_kernel<Real><<<(g.cap_h + 255) / 256, 256, 0, stream>>>(rec[cur ^ 1], &sd->zero, &sd->c_first1, g.cap_h, send_l, sd);
+        ++launches;
+        PS_CUDA_TRY(err, cudaGetLastError());
+        return PS_OK;
+    }
+
+    // stage 4 (recv_r holds the right rank's M2, if any): finish the sub-step
+    int stage_finish() {
+        if (g.gr) {
+            slab_unpack_kernel<Real><<<(g.cap_h + 255) / 256, 256, 0, stream>>>(recv_r, rec[cur ^ 1], &sd->c_last2, &sd->c_last1, g.cap_h, sd);
+            ++launches;
+        }
+        PS_CUDA_TRY(err, cudaGetLastError());
+        cur ^= 1;
+        last = h_step;
+        ++substeps_done;
+        return PS_OK;
+    }
+
+    // One process per GPU: the stages above with NCCL send / recv between x-neighbours.
+    int substep() {
+        const NcclApi& api = nccl_api();
+        const size_t hb = halo_msg_bytes();
+        cudaStream_t st = stream;
+        int rc;
+        if ((rc = stage_bin())) return rc;
+        if (nranks > 1) {                                                         // ---- M0: migrants + halo, both ways
+            if ((rc = nccl_try(api.GroupStart(), "ncclGroupStart"))) return rc;
+            if (g.gl) { api.Send(send_l, hb, kNcclUint8, rank - 1, comm, st); api.Recv(recv_l, hb, kNcclUint8, rank - 1, comm, st); }
+            if (g.gr) { api.Send(send_r, hb, kNcclUint8, rank + 1, comm, st); api.Recv(recv_r, hb, kNcclUint8, rank + 1, comm, st); }
+            if ((rc = nccl_try(api.GroupEnd(), "ncclGroupEnd (M0)"))) return rc;
+        }
+        if ((rc = stage_build())) return rc;
+        const bool send_now = send_now_step;
+        if (send_now && (rc = pack_m1())) return rc;
+        if (nranks > 1) {                                                         // ---- M1: boundary states to the right
             if ((rc = nccl_try(api.GroupStart(), "ncclGroupStart"))) return rc;
             if (send_now) api.Send(send_r, hb, kNcclUint8, rank + 1, comm, st);
             if (g.gl) api.Recv(recv_l, hb, kNcclUint8, rank - 1, comm, st);
             if ((rc = nccl_try(api.GroupEnd(), "ncclGroupEnd (M1)"))) return rc;
         }
-        if (g.gl) {                                                               // ---- phase B
-            slab_unpack_kernel<Real><<<g_hh, 256, 0, st>>>(recv_l, rec[nw], &sd->zero, &sd->c_first2, g.cap_h, sd);
-            slab_unblock_kernel<<<(h.c_first2 + 255) / 256 + 1, 256, 0, st>>>(head, brem, entries, wl[r0 % 3], &ds->wl_count[r0 % 3], r0, sd);
-            launches += 2;
-            if ((rc = launch_resolve(k, r0))) return rc;
-        }
+        if (g.gl && (rc = stage_phase_b())) return rc;
         if (g.gr && !send_now) {                                                  // rare: our right boundary depended on the left one
-            slab_pack_kernel<Real><<<g_hh, 256, 0, st>>>(rec[nw], &sd->c_last2, &sd->n_local, g.cap_h, send_r, sd); ++launches;
+            if ((rc = pack_m1())) return rc;
             if ((rc = nccl_try(api.Send(send_r, hb, kNcclUint8, rank + 1, comm, st), "ncclSend (late M1)"))) return rc;
         }
-        // ---- M2: the left ghost column's final states return to the left rank (its last own column)
-        if (g.gl) { slab_pack_kernel<Real><<<g_hh, 256, 0, st>>>(rec[nw], &sd->zero, &sd->c_first1, g.cap_h, send_l, sd); ++launches; }
-        if (nranks > 1) {
+        if (g.gl && (rc = pack_m2())) return rc;
+        if (nranks > 1) {                                                         // ---- M2: ghost states back to the left
             if ((rc = nccl_try(api.GroupStart(), "ncclGroupStart"))) return rc;
             if (g.gl) api.Send(send_l, hb, kNcclUint8, rank - 1, comm, st);
             if (g.gr) api.Recv(recv_r, hb, kNcclUint8, rank + 1, comm, st);
             if ((rc = nccl_try(api.GroupEnd(), "ncclGroupEnd (M2)"))) return rc;
         }
-        if (g.gr) { slab_unpack_kernel<Real><<<g_hh, 256, 0, st>>>(recv_r, rec[nw], &sd->c_last2, &sd->c_last1, g.cap_h, sd); ++launches; }
-        PS_CUDA_TRY(err, cudaGetLastError());
-        cur = nw;
-        last = h;
-        ++substeps_done;
-        return PS_OK;
+        return stage_finish();
     }
+
 
     int sync() {
         if (err.status != PS_OK) return err.status;
@@ -634,6 +685,62 @@ struct SlabCollider {
         out->rounds_total = hc->ds.rounds_total;
         out->max_cell_count = hc->ds.max_cell;
         out->kernel_launches = launches;
+        return PS_OK;
+    }
+};
+
+// Several ranks of one scene emulated in ONE process on ONE GPU: the same per-rank stages, with device-to-device
+// copies where the multi-process path has NCCL messages, driven in rank order (so the hand-over chain of a
+// sub-step simply runs left to right).  This is how the slab protocol is tested on a single-GPU box.
+template <class Real>
+struct SlabGroupLocal {
+    std::vector<SlabCollider<Real>*> ranks;
+    Error err;
+
+    ~SlabGroupLocal() { for (auto* r : ranks) { r->destroy(); delete r; } }
+
+    int create(const ps_config& cfg, int nranks, uint32_t rows, uint32_t cols) {
+        for (int r = 0; r < nranks; ++r) {
+            auto* c = new SlabCollider<Real>();
+            ranks.push_back(c);
+            const int rc = c->create(cfg, r, nranks, nullptr, rows, cols);
+            if (rc != PS_OK) { err = c->err; return rc; }
+        }
+        return PS_OK;
+    }
+
+    int copy(void* dst, SlabCollider<Real>* to, const void* src, SlabCollider<Real>* from) {
+        // the source was written on `from`'s stream: wait for it, then copy on the receiver's stream
+        PS_CUDA_TRY(err, cudaStreamSynchronize(from->stream));
+        PS_CUDA_TRY(err, cudaMemcpyAsync(dst, src, from->halo_msg_bytes(), cudaMemcpyDeviceToDevice, to->stream));
+        return PS_OK;
+    }
+
+    int substep() {
+        const int n = (int)ranks.size();
+        int rc;
+        for (auto* r : ranks) if ((rc = r->stage_bin())) { err = r->err; return rc; }
+        for (int k = 0; k < n; ++k) {                                               // M0
+            if (k > 0 && (rc = copy(ranks[k - 1]->recv_r, ranks[k - 1], ranks[k]->send_l, ranks[k]))) return rc;
+            if (k + 1 < n && (rc = copy(ranks[k + 1]->recv_l, ranks[k + 1], ranks[k]->send_r, ranks[k]))) return rc;
+        }
+        for (auto* r : ranks) if ((rc = r->stage_build())) { err = r->err; return rc; }
+        for (int k = 0; k < n; ++k) {                                               // M1 chain, left to right
+            auto* r = ranks[k];
+            if (k > 0 && (rc = r->stage_phase_b())) { err = r->err; return rc; }
+            if (k + 1 < n) {
+                if ((rc = r->pack_m1())) { err = r->err; return rc; }
+                if ((rc = copy(ranks[k + 1]->recv_l, ranks[k + 1], r->send_r, r))) return rc;
+            }
+        }
+        for (int k = n - 1; k >= 0; --k) {                                          // M2, right to left
+            auto* r = ranks[k];
+            if (k > 0) {
+                if ((rc = r->pack_m2())) { err = r->err; return rc; }
+                if ((rc = copy(ranks[k - 1]->recv_r, ranks[k - 1], r->send_l, r))) return rc;
+            }
+        }
+        for (auto* r : ranks) if ((rc = r->stage_finish())) { err = r->err; return rc; }
         return PS_OK;
     }
 };

@@ -56,6 +56,43 @@ def test_device_spawner_matches_host_generator():
     assert_bit_exact(got_v, vel0)
 
 
+@pytest.mark.parametrize("nranks,precision,t_acc,seed", [(2, "f64", False, 1), (3, "f32", True, 2), (4, "f64", True, 3), (8, "f32", False, 4)])
+def test_ranks_emulated_on_one_gpu_equal_oracle(nranks, precision, t_acc, seed):
+    """The whole multi-rank protocol (migration, halo, blocked boundary particles, M1 / M2 hand-over) with all
+    ranks in one process on one GPU (SlabGroup): same kernels as the NCCL path, device copies for messages."""
+    from particle_simulator_b200 import SlabGroup
+
+    dtype = np.float64 if precision == "f64" else np.float32
+    scene = scenes.default_scene()
+    pos0, vel0 = scenes.spawn(scene, seed=seed)
+    want_p, want_v, out = run_oracle(scene, pos0.astype(dtype), vel0.astype(dtype), 300, collisions=True, t_acc=t_acc)
+    with SlabGroup(scene, nranks, precision=precision, contacts_per_particle=32) as g:
+        g.upload_global(pos0, vel0)
+        g.set_acc(t_acc)
+        g.step_substeps(300)
+        parts = [g.download_owned(r) for r in range(nranks)]
+        pairs = sum(g.stats(r)["pairs_total"] for r in range(nranks))
+    got_p, got_v = gather(parts, scene.count, dtype)
+    assert pairs == out["stats"]["pairs_total"]
+    assert_bit_exact(got_p, want_p, "positions")
+    assert_bit_exact(got_v, want_v, "velocities")
+
+
+def test_emulated_ranks_dense_narrow_slabs():
+    from particle_simulator_b200 import SlabGroup
+
+    scene = scenes.Scene(count=3000, width=64.0, height=400.0)       # 16 columns, 4 ranks: 4 columns each, ~1.9 particles per cell
+    pos0, vel0 = scenes.spawn(scene, seed=5)
+    want_p, want_v, out = run_oracle(scene, pos0, vel0, 120, collisions=True, t_acc=False)
+    with SlabGroup(scene, 4, precision="f64", contacts_per_particle=64) as g:
+        g.upload_global(pos0, vel0)
+        g.step_substeps(120)
+        parts = [g.download_owned(r) for r in range(4)]
+    got_p, got_v = gather(parts, scene.count, np.float64)
+    assert_bit_exact(got_p, want_p, "positions")
+    assert_bit_exact(got_v, want_v, "velocities")
+
+
 def _two_rank_worker(rank, world, port, tmpdir, case):
     import torch
     import torch.distributed as dist
