@@ -93,8 +93,9 @@ struct DevState {
     uint32_t rounds_last;
     uint32_t pad;
     unsigned long long pairs_total, rounds_total;
+    uint32_t dbg[4];           // first offending slot / cell when FLAG_CORRUPT is raised
 };
-constexpr uint32_t FLAG_CELL_OVERFLOW = 1u, FLAG_CAPACITY = 2u;
+constexpr uint32_t FLAG_CELL_OVERFLOW = 1u, FLAG_CAPACITY = 2u, FLAG_CORRUPT = 4u;
 
 // contact-list entry: partner slot (28 bits) | offset index (3 bits) | role (1 = this particle is the centre)
 constexpr uint32_t ENT_SLOT_MASK = (1u << 28) - 1;
@@ -325,6 +326,10 @@ detect_kernel(const Rec<Real>* __restrict__ rec, const uint32_t* __restrict__ ce
             const uint32_t gj = fj > (Real)0 ? (fj < (Real)k.rows ? (uint32_t)fj : k.rows - 1) : 0u;
             const uint32_t lx = gi - sv.col_off;
             c = lx * k.rows + gj;
+            if (lx >= sv.ncl) {                                  // a record outside the local grid: corrupt state, stop before indexing with it
+                if (!atomicOr(&ds->flags, FLAG_CORRUPT)) { ds->dbg[0] = a; ds->dbg[1] = gi; ds->dbg[2] = gj; ds->dbg[3] = n; }
+                c = 0;
+            }
             a_own = lx >= sv.gl && lx < sv.ncl - sv.gr;
             l_own = lx >= 1u && (lx - 1u) >= sv.gl && (lx - 1u) < sv.ncl - sv.gr;
             r_own = (lx + 1u) >= sv.gl && (lx + 1u) < sv.ncl - sv.gr;

@@ -22,6 +22,7 @@
 // ncclSend / ncclRecv between x-neighbours inside one ncclGroup per exchange (NVLink 5 / NVSwitch);
 // messages are a few hundred KB, so the cost is latency: one host synchronisation per sub-step.
 #pragma once
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -54,6 +55,8 @@ struct SlabDev {               // device-side counters, copied to the host once 
     uint32_t err;
     uint32_t n_own_prev;       // owned particles at the start of this sub-step
     uint32_t zero;             // always 0 (range start for the pack / unpack kernels)
+    uint32_t own_b_prev;       // first owned slot of the layout this sub-step started from
+    uint32_t pad[3];
 };
 
 // halo / migration message: header + records + particle indices
@@ -130,6 +133,7 @@ __global__ void __launch_bounds__(256)
 slab_begin_kernel(SlabDev* __restrict__ sd, DevState* __restrict__ ds, void* send_l, void* send_r) {
     if (threadIdx.x == 0 && blockIdx.x == 0) {
         sd->n_own_prev = sd->own_e - sd->own_b;
+        sd->own_b_prev = sd->own_b;
         sd->right_incomplete = 0;
         ds->entries_used = 0;
         reinterpret_cast<HaloHeader*>(send_l)->count = 0;
@@ -145,7 +149,7 @@ slab_bin_kernel(const Rec<Real>* __restrict__ rec_old, const uint32_t* __restric
                 void* send_l, void* send_r, SlabDev* __restrict__ sd, DevState* __restrict__ ds) {
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= sd->n_own_prev) return;
-    const uint32_t s = sd->own_b + t;
+    const uint32_t s = sd->own_b_prev + t;
     Rec<Real> r = ld_rec(rec_old + s);
     if (!ds->flags) integrate_rec<Real>(r, k);                      // error state: the state stays frozen
     uint32_t gi, gj;
@@ -216,7 +220,7 @@ __global__ void slab_counts_kernel(const uint32_t* __restrict__ cell_start, Slab
 
 template <class Real>
 __device__ __forceinline__ uint32_t slab_input_pid(uint32_t t, const uint32_t* pid_old, const SlabDev* sd, const SlabGeom& g, void* recv_l, void* recv_r) {
-    if (t < g.cap) return pid_old[sd->own_b + t];
+    if (t < g.cap) return pid_old[sd->own_b_prev + t];
     const uint32_t j = t - g.cap;
     return j < g.cap_h ? halo_pids<Real>(recv_l, g.cap_h)[j] : halo_pids<Real>(recv_r, g.cap_h)[j - g.cap_h];
 }
@@ -252,7 +256,7 @@ slab_move_kernel(const Rec<Real>* __restrict__ rec_old, const uint32_t* __restri
     for (uint32_t q = b; q < e; ++q) rank += tmp_id[q] < id ? 1u : 0u;       // ascending particle index inside the cell (:146-158)
     Rec<Real> r;
     if (t < g.cap) {
-        r = ld_rec(rec_old + sd->own_b + t);
+        r = ld_rec(rec_old + sd->own_b_prev + t);
         if (!ds->flags) integrate_rec<Real>(r, k);                           // same arithmetic as slab_bin_kernel, bit for bit
     } else {
         const uint32_t j = t - g.cap;
@@ -354,6 +358,14 @@ struct SlabCollider {
     void* stage = nullptr; size_t stage_bytes = 0;
 
     int fail(int status, const std::string& text) { err.status = status; err.text = text; return status; }
+    // PS_SLAB_DEBUG=1: synchronise after every stage kernel and name the one that faulted
+    bool debug_sync = getenv("PS_SLAB_DEBUG") != nullptr;
+    int dbg(const char* what) {
+        if (!debug_sync) return PS_OK;
+        const cudaError_t e = cudaStreamSynchronize(stream);
+        if (e != cudaSuccess) return fail(PS_ERR_CUDA, std::string("rank ") + std::to_string(rank) + " after " + what + ": " + cudaGetErrorString(e));
+        return PS_OK;
+    }
     int nccl_try(int rc, const char* what) {
         if (rc == kNcclSuccess) return PS_OK;
         const NcclApi& api = nccl_api();
@@ -520,6 +532,10 @@ struct SlabCollider {
         if (e & SLAB_ERR_MIGRATION) return fail(PS_ERR_MIGRATION, "a particle crossed a whole neighbouring slab in one sub-step");
         if (e & SLAB_ERR_HALO) return fail(PS_ERR_CAPACITY, "halo / migration buffer too small for this scene");
         if (e & SLAB_ERR_CAPACITY) return fail(PS_ERR_CAPACITY, "this rank's slab holds more particles than it was sized for");
+        if (hc->ds.flags & FLAG_CORRUPT) return fail(PS_ERR_CUDA, "rank " + std::to_string(rank) + ": slot " + std::to_string(hc->ds.dbg[0]) + " of " + std::to_string(hc->ds.dbg[3]) +
+                                                     " holds a record in global cell (" + std::to_string(hc->ds.dbg[1]) + "," + std::to_string(hc->ds.dbg[2]) + "), outside local columns [" +
+                                                     std::to_string(g.col_off) + "," + std::to_string(g.col_off + g.ncl) + "); sd.err=" + std::to_string(hc->sd.err) +
+                                                     " n_own_prev=" + std::to_string(hc->sd.n_own_prev) + " own=[" + std::to_string(hc->sd.own_b) + "," + std::to_string(hc->sd.own_e) + ")");
         if (hc->ds.flags & FLAG_CAPACITY) return fail(PS_ERR_CAPACITY, "contact list exceeded its capacity; raise ps_config.contacts_per_particle");
         if (hc->ds.flags & FLAG_CELL_OVERFLOW) return fail(PS_ERR_CELL_OVERFLOW, "a grid cell held more than 255 particles (src/core.zig:51,132)");
         return PS_OK;
@@ -553,16 +569,24 @@ struct SlabCollider {
         const unsigned g_cap = (g.cap + 255) / 256, g_in = (g.cap + 2 * g.cap_h + 255) / 256, g_h = (2 * g.cap_h + 255) / 256;
         cudaStream_t st = stream;
         const StepConst<Real>& k = k_step;
+        if (int d = dbg("bin")) return d;
         slab_bin_recv_kernel<Real><<<g_h, 256, 0, st>>>(recv_l, recv_r, k, g, cell_count, slot_cell, arrival, sd, ds);
+        if (int d = dbg("bin_recv")) return d;
         PS_CUDA_TRY(err, exclusive_scan_u32(cell_count, cell_start, ncell_local, scan_sums, cell_start + ncell_local, &ds->max_cell, st));
+        if (int d = dbg("scan")) return d;
         slab_counts_kernel<<<1, 32, 0, st>>>(cell_start, g, sd);
+        if (int d = dbg("counts")) return d;
         slab_place_kernel<Real><<<g_in, 256, 0, st>>>(slot_cell, arrival, pid[cur], cell_start, g, recv_l, recv_r, sd, tmp_id);
+        if (int d = dbg("place")) return d;
         slab_move_kernel<Real><<<g_in, 256, 0, st>>>(rec[cur], pid[cur], slot_cell, cell_start, tmp_id, k, g, recv_l, recv_r, sd, ds, rec[nw], pid[nw]);
+        if (int d = dbg("move")) return d;
         SlabView sv{g.gl, g.gr, g.ncl, g.col_off, g.gcols, &sd->n_local, &sd->n_blocked, brem};
         detect_kernel<Real, true><<<g_cap, 256, 0, st>>>(rec[nw], cell_start, 0u, k, entries, entries_cap, head, wl[0], ds, sv);
         launches += 9;
         int rc;
+        if (int d = dbg("detect")) return d;
         if ((rc = launch_resolve(k, 0u))) return rc;                              // phase A
+        if (int d = dbg("resolve A")) return d;
         if (g.gr) { slab_right_check_kernel<<<g_cap, 256, 0, st>>>(head, brem, sd); ++launches; }
         if ((rc = read_back())) return rc;                                        // the one host synchronisation of the sub-step
         h_step = hc->sd;
@@ -585,7 +609,9 @@ struct SlabCollider {
         slab_unpack_kernel<Real><<<(g.cap_h + 255) / 256, 256, 0, st>>>(recv_l, rec[cur ^ 1], &sd->zero, &sd->c_first2, g.cap_h, sd);
         slab_unblock_kernel<<<(h_step.c_first2 + 255) / 256 + 1, 256, 0, st>>>(head, brem, entries, wl[r0_step % 3], &ds->wl_count[r0_step % 3], r0_step, sd);
         launches += 2;
-        return launch_resolve(k_step, r0_step);
+        if (int d = dbg("unpack+unblock")) return d;
+        if (int rc = launch_resolve(k_step, r0_step)) return rc;
+        return dbg("resolve B");
     }
 
     // M2 out: the left ghost column's final states -> send_l (the left rank's last own column)
