@@ -103,6 +103,11 @@ int ps_upload(ps_sim* sim, const double* pos_xy, const double* vel_xy);      /* 
 int ps_upload_f32(ps_sim* sim, const float* pos_xy, const float* vel_xy);
 int ps_download(ps_sim* sim, double* pos_xy, double* vel_xy);                /* either may be NULL */
 int ps_download_f32(ps_sim* sim, float* pos_xy, float* vel_xy);              /* pos = the GUI's @floatCast, src/main.zig:104-105 */
+/* Spawner.spawnRandom (src/core.zig:395-410) on the device: x ~ U[radius, width), y ~ U[radius, height),
+ * velocity components ~ U[vel_min, vel_max), from a counter-based generator (splitmix64 of seed and particle
+ * index; the reference's std.Random stream is seeded from the wall clock and is not reproduced).  Bit-identical
+ * to the host generator in scenes.py / core_cuda.hpp, so no host arrays are needed for large scenes. */
+int ps_spawn(ps_sim* sim, uint64_t seed, double vel_min, double vel_max);
 /* particles.accelerations (src/core.zig:16): a pure function of t_acc and g (:249-257). */
 int ps_download_acc(ps_sim* sim, double* acc_xy);
 

@@ -78,6 +78,7 @@ SYMBOLS = {
     "ps_download": (ctypes.c_int, [_P, _P, _P]),
     "ps_download_f32": (ctypes.c_int, [_P, _P, _P]),
     "ps_download_acc": (ctypes.c_int, [_P, _P]),
+    "ps_spawn": (ctypes.c_int, [_P, _U64, ctypes.c_double, ctypes.c_double]),
     "ps_step": (ctypes.c_int, [_P, _U64]),
     "ps_step_substeps": (ctypes.c_int, [_P, _U64]),
     "ps_toggle_acc": (ctypes.c_int, [_P]),

@@ -161,6 +161,12 @@ class Simulation:
         _check(fn(self._h, self._ptr(pos), self._ptr(vel)), self._h)
         return pos, vel
 
+    def spawn(self, seed: int, vel_min: float | None = None, vel_max: float | None = None) -> None:
+        """Spawner.spawnRandom on the device (same values as scenes.spawn(scene, seed))."""
+        vmin = self.scene.vel_min if vel_min is None else vel_min
+        vmax = self.scene.vel_max if vel_max is None else vel_max
+        _check(self._L.ps_spawn(self._h, seed, vmin, vmax), self._h)
+
     def download_acc(self, acc=None):
         if acc is None:
             acc = np.empty((self.count, 2), dtype=np.float64)

@@ -48,6 +48,7 @@ struct ps_sim {
     virtual int stats(ps_stats* out) = 0;
     virtual int check_deferred() = 0;
     virtual double dt() const = 0;
+    virtual int spawn(uint64_t seed, double vmin, double vmax) = 0;
 
     int ensure_stage(uint64_t bytes) {
         if (bytes <= stage_bytes) return PS_OK;
@@ -248,6 +249,19 @@ struct SimT final : ps_sim {
     }
 
     double dt() const override { return (double)ps::make_step_const<Real>(cfg, false, rows, cols).dt; }
+
+    int spawn(uint64_t seed, double vmin, double vmax) override {
+        DeviceGuard g(device);
+        if (n == 0) return PS_OK;
+        uint64_t z = seed + 0x9E3779B97F4A7C15ull;           // splitmix64(seed): the generator's stream base (scenes.py uniform01)
+        z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull; z = (z ^ (z >> 27)) * 0x94D049BB133111EBull; z ^= z >> 31;
+        ps::spawn_soa_kernel<Real><<<148 * 16, 256, 0, stream>>>(n, z, cfg.radius, cfg.width, cfg.height, vmin, vmax, px, py, vx, vy);
+        ++launches;
+        PS_CUDA_TRY(err, cudaGetLastError());
+        if (cfg.collisions) col.invalidate_records();
+        PS_CUDA_TRY(err, cudaStreamSynchronize(stream));
+        return PS_OK;
+    }
 };
 
 int validate(const ps_config* cfg, uint32_t* rows, uint32_t* cols, std::string* why) {
@@ -328,6 +342,8 @@ int ps_upload(ps_sim* s, const double* pos, const double* vel) { return s ? s->u
 int ps_upload_f32(ps_sim* s, const float* pos, const float* vel) { return s ? s->upload(pos, vel, false) : PS_ERR_BAD_ARG; }
 int ps_download(ps_sim* s, double* pos, double* vel) { return s ? s->download(pos, vel, true) : PS_ERR_BAD_ARG; }
 int ps_download_f32(ps_sim* s, float* pos, float* vel) { return s ? s->download(pos, vel, false) : PS_ERR_BAD_ARG; }
+
+int ps_spawn(ps_sim* s, uint64_t seed, double vel_min, double vel_max) { return s ? s->spawn(seed, vel_min, vel_max) : PS_ERR_BAD_ARG; }
 
 int ps_download_acc(ps_sim* s, double* acc_xy) {
     if (!s || !acc_xy) return PS_ERR_BAD_ARG;

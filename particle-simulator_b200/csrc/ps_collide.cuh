@@ -358,7 +358,7 @@ detect_kernel(const Rec<Real>* __restrict__ rec, const uint32_t* __restrict__ ce
             test(st.m0, st.m3);
             if (st.right) test(st.r0, st.r3);
             // own-cell partners appear twice in a's sub-list (a as neighbour and a as centre, Q1)
-            if (!SLAB) {
+            if (!SLAB || (a_own && l_own && r_own)) {            // every column of the block is an own column: nothing to filter
                 cnt = (uint32_t)__popcll(mask) + (uint32_t)__popcll(range_bits(mask, nL + (st.m1 - st.m0), st.m2 - st.m1));
             } else {
                 if (l_own) cnt += (uint32_t)__popcll(range_bits(mask, 0u, st.l2 - st.l0));                       // a neighbour of left-column centres
@@ -394,7 +394,7 @@ detect_kernel(const Rec<Real>* __restrict__ rec, const uint32_t* __restrict__ ce
         return;
     }
     head[a] = head_word(0u, blocked ? 0u : cnt, begin);
-    if (SLAB) sv.brem[a] = blocked ? cnt : 0u;
+    if (SLAB && blocked) sv.brem[a] = cnt;                   // brem is zero everywhere else (cleared at creation and by the unblock kernel)
     if (!cnt) return;
     uint32_t w = begin;
     if (!wide) {

@@ -22,6 +22,7 @@
 // ncclSend / ncclRecv between x-neighbours inside one ncclGroup per exchange (NVLink 5 / NVSwitch);
 // messages are a few hundred KB, so the cost is latency: one host synchronisation per sub-step.
 #pragma once
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <vector>
@@ -124,6 +125,20 @@ slab_spawn_kernel(uint64_t n_total, uint64_t seed_base, double radius, double wi
         if (s >= g.cap) { atomicOr(&sd->err, SLAB_ERR_CAPACITY); continue; }
         st_rec(rec + s, Rec<Real>{rx, (Real)y, (Real)u, (Real)w});
         pid[s] = (uint32_t)i;
+    }
+}
+
+// The same generator writing a whole scene into SoA arrays in index order (single-GPU handle, ps_spawn).
+template <class Real>
+__global__ void __launch_bounds__(256)
+spawn_soa_kernel(uint64_t n, uint64_t seed_base, double radius, double width, double height, double vmin, double vmax,
+                 Real* __restrict__ px, Real* __restrict__ py, Real* __restrict__ vx, Real* __restrict__ vy) {
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        px[i] = (Real)(radius + (width - radius) * uniform01_dev(seed_base, i, 0));
+        py[i] = (Real)(radius + (height - radius) * uniform01_dev(seed_base, i, 1));
+        vx[i] = (Real)(vmin + (vmax - vmin) * uniform01_dev(seed_base, i, 2));
+        vy[i] = (Real)(vmin + (vmax - vmin) * uniform01_dev(seed_base, i, 3));
     }
 }
 
@@ -366,6 +381,39 @@ struct SlabCollider {
         if (e != cudaSuccess) return fail(PS_ERR_CUDA, std::string("rank ") + std::to_string(rank) + " after " + what + ": " + cudaGetErrorString(e));
         return PS_OK;
     }
+    // PS_SLAB_TIMING=1: CUDA-event time of every stage of the sub-step, summed and printed when the handle is destroyed
+    bool timing = getenv("PS_SLAB_TIMING") != nullptr;
+    static constexpr int kTicks = 9;
+    static constexpr uint64_t kTimingSkip = 8;
+    cudaEvent_t ev[kTicks] = {};
+    bool ev_set[kTicks] = {};
+    double acc_ms[kTicks] = {};
+    double host_wait_ms = 0;
+    void tick(int i) {
+        if (!timing) return;
+        if (!ev[i]) cudaEventCreate(&ev[i]);
+        cudaEventRecord(ev[i], stream);
+        ev_set[i] = true;
+    }
+    void tock() {
+        if (!timing) return;
+        cudaStreamSynchronize(stream);
+        if (substeps_done <= kTimingSkip) { for (int i = 0; i < kTicks; ++i) { acc_ms[i] = 0; ev_set[i] = false; } return; }   // connection set-up, first sort
+        int prev = -1;
+        for (int i = 0; i < kTicks; ++i) {
+            if (!ev_set[i]) continue;
+            if (prev >= 0) { float ms = 0; cudaEventElapsedTime(&ms, ev[prev], ev[i]); acc_ms[i] += ms; }
+            prev = i; ev_set[i] = false;
+        }
+    }
+    void report() {
+        if (!timing || substeps_done <= kTimingSkip) return;
+        const double nsub = (double)(substeps_done - kTimingSkip);
+        static const char* names[kTicks] = {"", "bin", "M0", "sort+detect", "resolve A+check", "readback", "M1", "phase B", "M2+finish"};
+        std::string line = "[slab timing] rank " + std::to_string(rank) + " per sub-step (us):";
+        for (int i = 1; i < kTicks; ++i) line += std::string(" ") + names[i] + "=" + std::to_string((int)(acc_ms[i] * 1e3 / nsub));
+        fprintf(stderr, "%s\n", line.c_str());
+    }
     int nccl_try(int rc, const char* what) {
         if (rc == kNcclSuccess) return PS_OK;
         const NcclApi& api = nccl_api();
@@ -438,6 +486,7 @@ struct SlabCollider {
 
     void destroy() {
         if (own_stream) cudaStreamSynchronize(own_stream);
+        report();
         if (comm) nccl_api().CommDestroy(comm);
         for (auto& r : rec) cudaFree(r);
         for (auto& p : pid) cudaFree(p);
@@ -585,9 +634,11 @@ struct SlabCollider {
         launches += 9;
         int rc;
         if (int d = dbg("detect")) return d;
+        tick(3);
         if ((rc = launch_resolve(k, 0u))) return rc;                              // phase A
         if (int d = dbg("resolve A")) return d;
         if (g.gr) { slab_right_check_kernel<<<g_cap, 256, 0, st>>>(head, brem, sd); ++launches; }
+        tick(4);
         if ((rc = read_back())) return rc;                                        // the one host synchronisation of the sub-step
         h_step = hc->sd;
         r0_step = hc->ds.rounds_last + 1;
@@ -641,14 +692,18 @@ struct SlabCollider {
         const size_t hb = halo_msg_bytes();
         cudaStream_t st = stream;
         int rc;
+        tick(0);
         if ((rc = stage_bin())) return rc;
+        tick(1);
         if (nranks > 1) {                                                         // ---- M0: migrants + halo, both ways
             if ((rc = nccl_try(api.GroupStart(), "ncclGroupStart"))) return rc;
             if (g.gl) { api.Send(send_l, hb, kNcclUint8, rank - 1, comm, st); api.Recv(recv_l, hb, kNcclUint8, rank - 1, comm, st); }
             if (g.gr) { api.Send(send_r, hb, kNcclUint8, rank + 1, comm, st); api.Recv(recv_r, hb, kNcclUint8, rank + 1, comm, st); }
             if ((rc = nccl_try(api.GroupEnd(), "ncclGroupEnd (M0)"))) return rc;
         }
+        tick(2);
         if ((rc = stage_build())) return rc;
+        tick(5);
         const bool send_now = send_now_step;
         if (send_now && (rc = pack_m1())) return rc;
         if (nranks > 1) {                                                         // ---- M1: boundary states to the right
@@ -657,7 +712,9 @@ struct SlabCollider {
             if (g.gl) api.Recv(recv_l, hb, kNcclUint8, rank - 1, comm, st);
             if ((rc = nccl_try(api.GroupEnd(), "ncclGroupEnd (M1)"))) return rc;
         }
+        tick(6);
         if (g.gl && (rc = stage_phase_b())) return rc;
+        tick(7);
         if (g.gr && !send_now) {                                                  // rare: our right boundary depended on the left one
             if ((rc = pack_m1())) return rc;
             if ((rc = nccl_try(api.Send(send_r, hb, kNcclUint8, rank + 1, comm, st), "ncclSend (late M1)"))) return rc;
@@ -669,7 +726,10 @@ struct SlabCollider {
             if (g.gr) api.Recv(recv_r, hb, kNcclUint8, rank + 1, comm, st);
             if ((rc = nccl_try(api.GroupEnd(), "ncclGroupEnd (M2)"))) return rc;
         }
-        return stage_finish();
+        rc = stage_finish();
+        tick(8);
+        tock();
+        return rc;
     }
 
 

@@ -200,3 +200,15 @@ def test_64m_particles_sampled_against_the_oracle():
     # clamp invariant over the whole set (src/core.zig:316)
     assert got_p[:, 0].min() >= 2.0 and got_p[:, 0].max() <= np.float32(scene.width) - np.float32(2.0)
     assert got_p[:, 1].min() >= 2.0 and got_p[:, 1].max() <= np.float32(scene.height) - np.float32(2.0)
+
+
+@pytest.mark.parametrize("precision", ["f64", "f32"])
+def test_device_spawner_equals_host_generator(precision):
+    """ps_spawn (Spawner.spawnRandom on the device) reproduces scenes.spawn bit for bit."""
+    scene = scenes.Scene(count=200_003, width=3000.0, height=1800.0)
+    want_p, want_v = scenes.spawn(scene, seed=11, dtype=DTYPES[precision])
+    with Simulation(scene, precision=precision, collisions=False) as sim:
+        sim.spawn(11)
+        got_p, got_v = sim.download(dtype=DTYPES[precision])
+    assert_bit_exact(got_p, want_p, "positions")
+    assert_bit_exact(got_v, want_v, "velocities")

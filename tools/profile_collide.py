@@ -22,23 +22,28 @@ ap.add_argument("--precision", default="f32")
 ap.add_argument("--warm-frames", type=int, default=1)
 ap.add_argument("--frames", type=int, default=1)
 ap.add_argument("--gravity", action="store_true")
+ap.add_argument("--spawn-on-device", action="store_true")
 args = ap.parse_args()
 
 scene = scenes.scaled_scene(args.particles)
 dt = np.float32 if args.precision == "f32" else np.float64
 n = args.particles
-pos = np.empty((n, 2), dtype=dt)
-vel = np.empty((n, 2), dtype=dt)
-chunk = 8 << 20
-for s in range(0, n, chunk):
-    m = min(chunk, n - s)
-    p, v = scenes.spawn(scene, seed=1, start=s, count=m, dtype=dt)
-    pos[s:s + m] = p
-    vel[s:s + m] = v
+if not args.spawn_on_device:
+    pos = np.empty((n, 2), dtype=dt)
+    vel = np.empty((n, 2), dtype=dt)
+    chunk = 8 << 20
+    for s in range(0, n, chunk):
+        m = min(chunk, n - s)
+        p, v = scenes.spawn(scene, seed=1, start=s, count=m, dtype=dt)
+        pos[s:s + m] = p
+        vel[s:s + m] = v
 torch.cuda.set_stream(torch.cuda.Stream())
 with Simulation(scene, precision=args.precision, collisions=True) as sim:
     sim.set_stream(torch.cuda.current_stream().cuda_stream)
-    sim.upload(pos, vel)
+    if args.spawn_on_device:
+        sim.spawn(1)
+    else:
+        sim.upload(pos, vel)
     sim.set_acc(args.gravity)
     sim.step(args.warm_frames)
     torch.cuda.synchronize()
