@@ -306,6 +306,9 @@ detect_kernel(const Rec<Real>* __restrict__ rec, const uint32_t* __restrict__ ce
               uint2* __restrict__ wl0, DevState* __restrict__ ds, SlabView sv) {
     __shared__ uint32_t sh_base, sh_wbase;
     const uint32_t a = blockIdx.x * blockDim.x + threadIdx.x;
+    // SLAB: `n` is the record capacity on entry; the slot count lives on the device.  The slot's position is
+    // requested before that count is known (any slot below the capacity may be read), so the two loads overlap.
+    const auto pa_early = a < n ? ld_pos(rec + a) : decltype(ld_pos(rec)){};
     if (SLAB) n = *sv.n_local;
     const bool valid = a < n;
     if (ds->flags) {                                         // error state (uniform: set by an earlier launch): no lists, no resolve
@@ -317,7 +320,7 @@ detect_kernel(const Rec<Real>* __restrict__ rec, const uint32_t* __restrict__ ce
     unsigned long long mask = 0ull;
     bool wide = false, a_own = true, l_own = true, r_own = true, blocked = false;
     if (valid) {
-        const auto pa = ld_pos(rec + a);
+        const auto pa = pa_early;
         uint32_t c;
         if (SLAB) {
             // local cell: global computeCoordinate, then shift by the slab's first local column

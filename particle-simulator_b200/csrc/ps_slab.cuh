@@ -159,26 +159,26 @@ slab_begin_kernel(SlabDev* __restrict__ sd, DevState* __restrict__ ds, void* sen
 // integrate + bounce, local cell + count for particles that stay in the local grid, migrants + halo into the send buffers
 template <class Real>
 __global__ void __launch_bounds__(256)
-slab_bin_kernel(const Rec<Real>* __restrict__ rec_old, const uint32_t* __restrict__ pid_old, StepConst<Real> k, SlabGeom g,
+slab_bin_kernel(const Rec<Real>* __restrict__ rec_old, const uint32_t* __restrict__ pid_old, uint32_t own_b_prev, uint32_t n_own_prev,
+                StepConst<Real> k, SlabGeom g,
                 uint32_t* __restrict__ cell_count, uint32_t* __restrict__ slot_cell, uint32_t* __restrict__ arrival,
                 void* send_l, void* send_r, SlabDev* __restrict__ sd, DevState* __restrict__ ds) {
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= sd->n_own_prev) return;
-    const uint32_t s = sd->own_b_prev + t;
+    if (t >= n_own_prev) return;                                     // the owned range is known on the host: no dependent load
+    const uint32_t s = own_b_prev + t;
     Rec<Real> r = ld_rec(rec_old + s);
     if (!ds->flags) integrate_rec<Real>(r, k);                      // error state: the state stays frozen
     uint32_t gi, gj;
     global_cell<Real>(r.x, r.y, k, g.gcols, gi, gj);
     if (gi < g.xlo || gi >= g.xhi) atomicOr(&sd->err, SLAB_ERR_MIGRATION);
-    const uint32_t id = pid_old[s];
     if (g.gl && gi <= g.x0) {                                        // migrant (gi < x0) or halo (gi == x0) for the left rank
         const uint32_t j = atomicAdd(&reinterpret_cast<HaloHeader*>(send_l)->count, 1u);
-        if (j < g.cap_h) { st_rec(halo_recs<Real>(send_l) + j, r); halo_pids<Real>(send_l, g.cap_h)[j] = id; }
+        if (j < g.cap_h) { st_rec(halo_recs<Real>(send_l) + j, r); halo_pids<Real>(send_l, g.cap_h)[j] = pid_old[s]; }
         else atomicOr(&sd->err, SLAB_ERR_HALO);
     }
     if (g.gr && gi + 1 >= g.x1) {                                    // migrant (gi >= x1) or halo (gi == x1-1) for the right rank
         const uint32_t j = atomicAdd(&reinterpret_cast<HaloHeader*>(send_r)->count, 1u);
-        if (j < g.cap_h) { st_rec(halo_recs<Real>(send_r) + j, r); halo_pids<Real>(send_r, g.cap_h)[j] = id; }
+        if (j < g.cap_h) { st_rec(halo_recs<Real>(send_r) + j, r); halo_pids<Real>(send_r, g.cap_h)[j] = pid_old[s]; }
         else atomicOr(&sd->err, SLAB_ERR_HALO);
     }
     if (gi >= g.col_off && gi < g.col_off + g.ncl) {                 // stays in the local grid (own or ghost column)
@@ -234,8 +234,8 @@ __global__ void slab_counts_kernel(const uint32_t* __restrict__ cell_start, Slab
 }
 
 template <class Real>
-__device__ __forceinline__ uint32_t slab_input_pid(uint32_t t, const uint32_t* pid_old, const SlabDev* sd, const SlabGeom& g, void* recv_l, void* recv_r) {
-    if (t < g.cap) return pid_old[sd->own_b_prev + t];
+__device__ __forceinline__ uint32_t slab_input_pid(uint32_t t, const uint32_t* pid_old, uint32_t own_b_prev, const SlabGeom& g, void* recv_l, void* recv_r) {
+    if (t < g.cap) return pid_old[own_b_prev + t];
     const uint32_t j = t - g.cap;
     return j < g.cap_h ? halo_pids<Real>(recv_l, g.cap_h)[j] : halo_pids<Real>(recv_r, g.cap_h)[j - g.cap_h];
 }
@@ -243,40 +243,40 @@ __device__ __forceinline__ uint32_t slab_input_pid(uint32_t t, const uint32_t* p
 template <class Real>
 __global__ void __launch_bounds__(256)
 slab_place_kernel(const uint32_t* __restrict__ slot_cell, const uint32_t* __restrict__ arrival, const uint32_t* __restrict__ pid_old,
-                  const uint32_t* __restrict__ cell_start, SlabGeom g, void* recv_l, void* recv_r,
-                  const SlabDev* __restrict__ sd, uint32_t* __restrict__ tmp_id) {
-    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= g.cap + 2 * g.cap_h || sd->err) return;
-    if (t < g.cap && t >= sd->n_own_prev) return;
+                  uint32_t own_b_prev, uint32_t n_own_prev, const uint32_t* __restrict__ cell_start, SlabGeom g, void* recv_l, void* recv_r,
+                  uint32_t* __restrict__ tmp_id) {
+    // input index space: [0, n_own_prev) own particles, [cap, cap + 2 cap_h) received records
+    uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n_own_prev) { t = g.cap + (t - n_own_prev); if (t >= g.cap + 2 * g.cap_h) return; }
     const uint32_t c = slot_cell[t];
     if (c == SLAB_INVALID) return;
     const uint32_t dst = cell_start[c] + arrival[t];
-    if (dst < g.cap) tmp_id[dst] = slab_input_pid<Real>(t, pid_old, sd, g, recv_l, recv_r);
+    if (dst < g.cap) tmp_id[dst] = slab_input_pid<Real>(t, pid_old, own_b_prev, g, recv_l, recv_r);
 }
 
 template <class Real>
 __global__ void __launch_bounds__(256)
-slab_move_kernel(const Rec<Real>* __restrict__ rec_old, const uint32_t* __restrict__ pid_old, const uint32_t* __restrict__ slot_cell,
-                 const uint32_t* __restrict__ cell_start, const uint32_t* __restrict__ tmp_id, StepConst<Real> k, SlabGeom g,
-                 void* recv_l, void* recv_r, const SlabDev* __restrict__ sd, const DevState* __restrict__ ds,
+slab_move_kernel(const Rec<Real>* __restrict__ rec_old, const uint32_t* __restrict__ pid_old, uint32_t own_b_prev, uint32_t n_own_prev,
+                 const uint32_t* __restrict__ slot_cell, const uint32_t* __restrict__ cell_start, const uint32_t* __restrict__ tmp_id,
+                 StepConst<Real> k, SlabGeom g, void* recv_l, void* recv_r, const DevState* __restrict__ ds,
                  Rec<Real>* __restrict__ rec_new, uint32_t* __restrict__ pid_new) {
-    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= g.cap + 2 * g.cap_h || sd->err) return;
-    if (t < g.cap && t >= sd->n_own_prev) return;
+    uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n_own_prev) { t = g.cap + (t - n_own_prev); if (t >= g.cap + 2 * g.cap_h) return; }
     const uint32_t c = slot_cell[t];
     if (c == SLAB_INVALID) return;
-    const uint32_t id = slab_input_pid<Real>(t, pid_old, sd, g, recv_l, recv_r);
+    const uint32_t id = slab_input_pid<Real>(t, pid_old, own_b_prev, g, recv_l, recv_r);
     const uint32_t b = cell_start[c], e = cell_start[c + 1];
     uint32_t rank = 0;
-    for (uint32_t q = b; q < e; ++q) rank += tmp_id[q] < id ? 1u : 0u;       // ascending particle index inside the cell (:146-158)
+    for (uint32_t q = b; q < e && q < g.cap; ++q) rank += tmp_id[q] < id ? 1u : 0u;   // ascending particle index inside the cell (:146-158)
     Rec<Real> r;
     if (t < g.cap) {
-        r = ld_rec(rec_old + sd->own_b_prev + t);
+        r = ld_rec(rec_old + own_b_prev + t);
         if (!ds->flags) integrate_rec<Real>(r, k);                           // same arithmetic as slab_bin_kernel, bit for bit
     } else {
         const uint32_t j = t - g.cap;
         r = j < g.cap_h ? ld_rec(halo_recs<Real>(recv_l) + j) : ld_rec(halo_recs<Real>(recv_r) + (j - g.cap_h));
     }
+    if (b + rank >= g.cap) return;                                           // only in an error state (capacity flagged by slab_counts_kernel)
     st_rec(rec_new + b + rank, r);
     pid_new[b + rank] = id;
 }
@@ -597,6 +597,7 @@ struct SlabCollider {
     SlabDev h_step{};
     uint32_t r0_step = 0;
     bool send_now_step = false;
+    uint32_t own_b_step = 0, n_own_step = 0;
     size_t halo_msg_bytes() const { return halo_bytes<Real>(g.cap_h); }
 
     // stage 1: integrate + bin own particles; send_l / send_r now hold the M0 messages
@@ -606,7 +607,8 @@ struct SlabCollider {
         cudaStream_t st = stream;
         PS_CUDA_TRY(err, cudaMemsetAsync(cell_count, 0, (size_t)ncell_local * sizeof(uint32_t), st));
         slab_begin_kernel<Real><<<1, 32, 0, st>>>(sd, ds, send_l, send_r);
-        slab_bin_kernel<Real><<<(g.cap + 255) / 256, 256, 0, st>>>(rec[cur], pid[cur], k_step, g, cell_count, slot_cell, arrival, send_l, send_r, sd, ds);
+        own_b_step = last.own_b; n_own_step = last.own_e - last.own_b;   // the layout left by the previous sub-step (host copy)
+        slab_bin_kernel<Real><<<(n_own_step + 255) / 256 + 1, 256, 0, st>>>(rec[cur], pid[cur], own_b_step, n_own_step, k_step, g, cell_count, slot_cell, arrival, send_l, send_r, sd, ds);
         launches += 2;
         PS_CUDA_TRY(err, cudaGetLastError());
         return PS_OK;
@@ -615,7 +617,7 @@ struct SlabCollider {
     // stage 2 (recv_l / recv_r hold the neighbours' M0): local sort, detect, phase A, one host synchronisation
     int stage_build() {
         const int nw = cur ^ 1;
-        const unsigned g_cap = (g.cap + 255) / 256, g_in = (g.cap + 2 * g.cap_h + 255) / 256, g_h = (2 * g.cap_h + 255) / 256;
+        const unsigned g_cap = (g.cap + 255) / 256, g_in = (n_own_step + 2 * g.cap_h + 255) / 256, g_h = (2 * g.cap_h + 255) / 256;
         cudaStream_t st = stream;
         const StepConst<Real>& k = k_step;
         if (int d = dbg("bin")) return d;
@@ -625,12 +627,14 @@ struct SlabCollider {
         if (int d = dbg("scan")) return d;
         slab_counts_kernel<<<1, 32, 0, st>>>(cell_start, g, sd);
         if (int d = dbg("counts")) return d;
-        slab_place_kernel<Real><<<g_in, 256, 0, st>>>(slot_cell, arrival, pid[cur], cell_start, g, recv_l, recv_r, sd, tmp_id);
+        slab_place_kernel<Real><<<g_in, 256, 0, st>>>(slot_cell, arrival, pid[cur], own_b_step, n_own_step, cell_start, g, recv_l, recv_r, tmp_id);
         if (int d = dbg("place")) return d;
-        slab_move_kernel<Real><<<g_in, 256, 0, st>>>(rec[cur], pid[cur], slot_cell, cell_start, tmp_id, k, g, recv_l, recv_r, sd, ds, rec[nw], pid[nw]);
+        slab_move_kernel<Real><<<g_in, 256, 0, st>>>(rec[cur], pid[cur], own_b_step, n_own_step, slot_cell, cell_start, tmp_id, k, g, recv_l, recv_r, ds, rec[nw], pid[nw]);
         if (int d = dbg("move")) return d;
         SlabView sv{g.gl, g.gr, g.ncl, g.col_off, g.gcols, &sd->n_local, &sd->n_blocked, brem};
-        detect_kernel<Real, true><<<g_cap, 256, 0, st>>>(rec[nw], cell_start, 0u, k, entries, entries_cap, head, wl[0], ds, sv);
+        const uint64_t n_hi = (uint64_t)n_own_step + 2ull * g.cap_h;             // at most this many local slots after the exchange
+        const unsigned g_det = (unsigned)(((n_hi < g.cap ? n_hi : g.cap) + 255) / 256);
+        detect_kernel<Real, true><<<g_det, 256, 0, st>>>(rec[nw], cell_start, g.cap, k, entries, entries_cap, head, wl[0], ds, sv);
         launches += 9;
         int rc;
         if (int d = dbg("detect")) return d;
