@@ -15,7 +15,10 @@
 //       the message is one contiguous range of records).  Until M1 arrives rank k+1 keeps those
 //       particles "blocked": pairs that involve them wait, everything else proceeds (phase A); then
 //       it unblocks them and finishes (phase B).
-//   M2  (leftward)  the final state of rank k+1's left ghost column returns to rank k, which owns it.
+//   After M1 the particles of rank k's last own column are simply KEPT by rank k+1 (it holds their final state
+//   as its left ghost column): ownership is handed over, rank k+1 integrates them at the next sub-step and routes
+//   them by their new column — those still in rank k's columns travel back inside the next M0 as ordinary
+//   migrants.  So there is no third message: a rank's owned slots are [0, start of its last own column).
 //
 // The result is bit-identical to the single-GPU / sequential reference order (the protocol is
 // modelled on the CPU in tests/_slab_model.py and checked against the oracle).  Transport is NCCL
@@ -224,8 +227,10 @@ __global__ void slab_counts_kernel(const uint32_t* __restrict__ cell_start, Slab
     const uint32_t n = cell_start[ncl * rows];
     sd->n_local = n;
     if (n > g.cap) atomicOr(&sd->err, SLAB_ERR_CAPACITY);
-    sd->own_b = cell_start[g.gl * rows];
-    sd->own_e = cell_start[(ncl - g.gr) * rows];
+    // owned after this sub-step: everything except the last own column and the right ghost column, which the right
+    // rank keeps (it finishes their pairs); the left ghost column, finished here, is ours
+    sd->own_b = 0u;
+    sd->own_e = g.gr ? cell_start[(ncl >= 2 ? ncl - 2 : 0) * rows] : n;
     sd->c_first1 = cell_start[ncl >= 1 ? rows : 0];
     sd->c_first2 = cell_start[(ncl >= 2 ? 2 : ncl) * rows];
     sd->c_last2 = cell_start[(ncl >= 2 ? ncl - 2 : 0) * rows];
@@ -303,7 +308,7 @@ slab_unblock_kernel(unsigned long long* __restrict__ head, uint32_t* __restrict_
     wl[atomicAdd(wl_count, 1u)] = make_uint2(a, entries[cur]);
 }
 
-// boundary hand-over (M1 / M2): a contiguous range of records with its length in front; fixed-size messages,
+// boundary hand-over (M1): a contiguous range of records with its length in front; fixed-size messages,
 // so that ranks that disagree about a count report SLAB_ERR_PROTOCOL instead of hanging inside NCCL
 template <class Real>
 __global__ void __launch_bounds__(256)
@@ -409,7 +414,7 @@ struct SlabCollider {
     void report() {
         if (!timing || substeps_done <= kTimingSkip) return;
         const double nsub = (double)(substeps_done - kTimingSkip);
-        static const char* names[kTicks] = {"", "bin", "M0", "sort+detect", "resolve A+check", "readback", "M1", "phase B", "M2+finish"};
+        static const char* names[kTicks] = {"", "bin", "M0", "sort+detect", "resolve A+check", "readback", "M1", "phase B", "finish"};
         std::string line = "[slab timing] rank " + std::to_string(rank) + " per sub-step (us):";
         for (int i = 1; i < kTicks; ++i) line += std::string(" ") + names[i] + "=" + std::to_string((int)(acc_ms[i] * 1e3 / nsub));
         fprintf(stderr, "%s\n", line.c_str());
@@ -641,7 +646,7 @@ struct SlabCollider {
         tick(3);
         if ((rc = launch_resolve(k, 0u))) return rc;                              // phase A
         if (int d = dbg("resolve A")) return d;
-        if (g.gr) { slab_right_check_kernel<<<g_cap, 256, 0, st>>>(head, brem, sd); ++launches; }
+        if (g.gr) { slab_right_check_kernel<<<(2 * g.cap_h + 255) / 256, 256, 0, st>>>(head, brem, sd); ++launches; }   // two columns of slots at most
         tick(4);
         if ((rc = read_back())) return rc;                                        // the one host synchronisation of the sub-step
         h_step = hc->sd;
@@ -669,20 +674,8 @@ struct SlabCollider {
         return dbg("resolve B");
     }
 
-    // M2 out: the left ghost column's final states -> send_l (the left rank's last own column)
-    int pack_m2() {
-        slab_pack_kernel<Real><<<(g.cap_h + 255) / 256, 256, 0, stream>>>(rec[cur ^ 1], &sd->zero, &sd->c_first1, g.cap_h, send_l, sd);
-        ++launches;
-        PS_CUDA_TRY(err, cudaGetLastError());
-        return PS_OK;
-    }
-
-    // stage 4 (recv_r holds the right rank's M2, if any): finish the sub-step
+    // stage 4: finish the sub-step (the new layout becomes current)
     int stage_finish() {
-        if (g.gr) {
-            slab_unpack_kernel<Real><<<(g.cap_h + 255) / 256, 256, 0, stream>>>(recv_r, rec[cur ^ 1], &sd->c_last2, &sd->c_last1, g.cap_h, sd);
-            ++launches;
-        }
         PS_CUDA_TRY(err, cudaGetLastError());
         cur ^= 1;
         last = h_step;
@@ -722,13 +715,6 @@ struct SlabCollider {
         if (g.gr && !send_now) {                                                  // rare: our right boundary depended on the left one
             if ((rc = pack_m1())) return rc;
             if ((rc = nccl_try(api.Send(send_r, hb, kNcclUint8, rank + 1, comm, st), "ncclSend (late M1)"))) return rc;
-        }
-        if (g.gl && (rc = pack_m2())) return rc;
-        if (nranks > 1) {                                                         // ---- M2: ghost states back to the left
-            if ((rc = nccl_try(api.GroupStart(), "ncclGroupStart"))) return rc;
-            if (g.gl) api.Send(send_l, hb, kNcclUint8, rank - 1, comm, st);
-            if (g.gr) api.Recv(recv_r, hb, kNcclUint8, rank + 1, comm, st);
-            if ((rc = nccl_try(api.GroupEnd(), "ncclGroupEnd (M2)"))) return rc;
         }
         rc = stage_finish();
         tick(8);
@@ -821,13 +807,6 @@ struct SlabGroupLocal {
             if (k + 1 < n) {
                 if ((rc = r->pack_m1())) { err = r->err; return rc; }
                 if ((rc = copy(ranks[k + 1]->recv_l, ranks[k + 1], r->send_r, r))) return rc;
-            }
-        }
-        for (int k = n - 1; k >= 0; --k) {                                          // M2, right to left
-            auto* r = ranks[k];
-            if (k > 0) {
-                if ((rc = r->pack_m2())) { err = r->err; return rc; }
-                if ((rc = copy(ranks[k - 1]->recv_r, ranks[k - 1], r->send_l, r))) return rc;
             }
         }
         for (auto* r : ranks) if ((rc = r->stage_finish())) { err = r->err; return rc; }

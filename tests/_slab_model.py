@@ -1,7 +1,7 @@
 """A rank-by-rank model of the multi-GPU slab protocol (test infrastructure).
 
 It mirrors, step for step, what particle-simulator_b200/csrc/ps_slab.cuh does on each GPU — the same
-messages (M0 migrants + halo, M1 boundary states to the right, M2 ghost states back to the left), the
+messages (M0 migrants + halo, M1 boundary states to the right, then ownership hand-over instead of a message back), the
 same ownership / filter / blocking rules — with the oracle's f64 arithmetic, so that the PROTOCOL can
 be checked on a CPU: R modelled ranks must reproduce the single-process oracle bit for bit.
 
@@ -59,7 +59,8 @@ class RankModel:
             oracle.run(self.params, p, v, 1, collisions=False, t_acc=self.t_acc)
         gx = self.gcol(p)
         # a particle may leave the slab by more than one column (integrate + the previous resolve's position
-        # corrections), but never past the neighbouring slab
+        # corrections), but never past the neighbouring slab.  Owned particles include the left ghost column of
+        # the previous sub-step (handed over by the left rank) and exclude the last own column (handed to the right).
         lo = slab_bounds(self.cols, self.nranks, self.rank - 1)[0] if self.gl else 0
         hi = slab_bounds(self.cols, self.nranks, self.rank + 1)[1] if self.gr else self.cols
         assert ((gx >= lo) & (gx < hi)).all(), "particle crossed a whole slab in one sub-step"
@@ -90,7 +91,8 @@ class RankModel:
         n = len(order)
         ncell = self.ncl * self.rows
         self.start = np.searchsorted(self.cell, np.arange(ncell + 3))
-        self.own_b, self.own_e = self.start[self.gl * self.rows], self.start[(self.ncl - self.gr) * self.rows]
+        # owned after the sub-step: all but the last own column and the right ghost column, which the right rank keeps
+        self.own_b, self.own_e = 0, (self.start[(self.ncl - 2) * self.rows] if self.gr else n)
         frozen = self.rec_p.copy()
         r2sq = (2 * self.scene.radius) ** 2
         rows, ncl, start = self.rows, self.ncl, self.start
@@ -207,16 +209,6 @@ class RankModel:
             self.blocked[a] = False
         self.W = [a for a in range(self.nblk) if self.head[a] < len(self.lists[a])]
 
-    def m2_out(self):      # left ghost column, final states
-        c0 = self.start[self.rows]
-        return self.rec_p[:c0].copy(), self.rec_v[:c0].copy(), self.ids[:c0].copy()
-
-    def m2_in(self, msg):  # final states of the last own column
-        p, v, ids = msg
-        b, e = self.start[(self.ncl - 2) * self.rows], self.start[(self.ncl - 1) * self.rows]
-        assert np.array_equal(ids, self.ids[b:e]), "M2 order mismatch"
-        self.rec_p[b:e] = p; self.rec_v[b:e] = v
-
     def finish(self):
         b, e = self.own_b, self.own_e
         self.pos, self.vel, self.pid = self.rec_p[b:e].copy(), self.rec_v[b:e].copy(), self.ids[b:e].copy()
@@ -239,8 +231,4 @@ def substep(model: RankModel, transport):
     if not sent:
         assert model.right_complete()
         transport.send(r, r + 1, model.m1_out())
-    if r > 0:
-        transport.send(r, r - 1, model.m2_out())                                                       # M2
-    if r < R - 1:
-        model.m2_in(transport.recv(r, r + 1))
-    model.finish()
+    model.finish()          # no third message: the right rank keeps the boundary column it has just finished
