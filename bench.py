@@ -48,6 +48,9 @@ def parse_args():
     ap.add_argument("--variant", type=int, default=0, help="integrate kernel variant (0 = auto)")
     ap.add_argument("--sweep", action="store_true", help="time every integrate kernel variant and print a table to stderr")
     ap.add_argument("--ref-sample", type=int, default=4 << 20, help="particles per step of the CPU reference arm")
+    ap.add_argument("--workload", default="integrate", choices=["integrate", "collide"],
+                    help="integrate = BASELINE.json configs[2] (default, the headline); collide = configs[4]: ONE 256 Mi-particle "
+                         "collision scene slab-decomposed over the ranks (strong scaling)")
     return ap.parse_args()
 
 
@@ -413,10 +416,78 @@ def run_extras(torch, sim, scene, hp, hv, n, S, prec):
     return out
 
 
+def run_collide(args):
+    """BASELINE.json configs[3]/[4]: one collision scene of --particles particles (default 256 Mi) on N GPUs.
+    N = 1: the single-GPU handle; N > 1: x-slabs, one process per GPU, NCCL send/recv of migrants, halo and
+    boundary states.  Strong scaling: the scene is the same for every N."""
+    import torch
+
+    from particle_simulator_b200 import Simulation, SlabSimulation, capi, scenes
+
+    rank, world, local = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)
+    capi.load(build_if_missing=False)
+    torch.cuda.set_device(local)
+    n = args.particles if args.particles != N_PER_GPU else 256 << 20
+    scene = scenes.scaled_scene(n)
+    K, W, S = args.steps, max(args.warmup, 3), scene.sub_steps
+    dist = None
+    if world > 1:
+        import torch.distributed as dist_mod
+
+        dist_mod.init_process_group("gloo")     # host-side channel only: NCCL id, barriers, max over ranks
+        dist = dist_mod
+        idt = torch.zeros(128, dtype=torch.uint8)
+        if rank == 0:
+            idt = torch.frombuffer(bytearray(SlabSimulation.unique_id()), dtype=torch.uint8).clone()
+        dist.broadcast(idt, 0)
+        sim = SlabSimulation(scene, rank, world, bytes(idt.numpy().tobytes()), precision=args.precision, device=local)
+    else:
+        sim = Simulation(scene, precision=args.precision, collisions=True, device=local)
+    sim.spawn(1)
+    clocks = ClockSampler(local)
+    for _ in range(W):
+        sim.step(1)
+    sim.sync()
+    if dist is not None:
+        dist.barrier()
+    torch.cuda.synchronize()
+    clocks.start()
+    t0 = time.perf_counter()
+    for _ in range(K):
+        sim.step(1)
+    sim.sync()
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    clocks.stop()
+    if dist is not None:
+        t = torch.tensor([dt], dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dt = float(t.item())
+    st = sim.stats()
+    launches = st["kernel_launches"]
+    sim.close()
+    if rank == 0:
+        line = {"metric": METRIC, "value": n * S * K / dt, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
+                "ms_per_step": 1e3 * dt / K, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+                "dtype": args.precision, "data": "synthetic",
+                "config": {"workload": f"{n >> 20}Mi particles, full updatePhysics with uniform-grid collisions (BASELINE.json configs[4]); "
+                                       f"step = one frame = 8 sub-steps; x-slab decomposition, NCCL send/recv halo + migration",
+                           "particles": n, "sub_steps": S, "timing": "host clock around K frames, sync on both sides, max over ranks"},
+                "gpu_launches": int(launches), "pairs_last_rank0": st["pairs_last"], "rounds_last_rank0": st["rounds_last"],
+                "clocks": clocks.summary()}
+        print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
 def main():
     args = parse_args()
     if args.impl == "reference":
         return run_reference(args)
+    if args.workload == "collide":
+        return run_collide(args)
     return run_ours(args)
 
 
