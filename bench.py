@@ -317,9 +317,9 @@ def run_ours(args):
     e2e = None
     if not args.no_e2e:
         def frame():
-            sim.upload(hp, hv)        # H2D of this frame's inputs (positions + velocities), pinned host memory
-            sim.step(1)               # Solver.updatePhysics
-            sim.download(ho, None)    # D2H of the frame's result: positions, what main.zig reads to draw
+            # Solver.updatePhysics on host slices: H2D of this frame's inputs (positions + velocities, pinned host memory
+            # in core.zig's f64 layout), the 8 sub-steps, D2H of the result (positions: what main.zig reads to draw)
+            sim.frame_host(hp, hv, ho, None, 1)
 
         ke = max(3, min(K, 10))
         timed(torch, dist, frame, 2)
@@ -327,7 +327,7 @@ def run_ours(args):
         e2e = {"value": n_total * S * ke / (ms_e * 1e-3), "unit": UNIT,
                "h2d_bytes_per_step": int(hp.nbytes + hv.nbytes), "d2h_bytes_per_step": int(ho.nbytes),
                "ms_per_step": ms_e / ke, "steps": ke,
-               "api": "ps_upload(f64 pos, vel) + ps_step(1) + ps_download(f64 pos), pinned host buffers"}
+               "api": "ps_frame_host(f64 pos_in, vel_in -> pos_out), pinned host buffers, chunked over 4 streams"}
     clocks.stop()
 
     extras = {}

@@ -115,6 +115,13 @@ int ps_download_acc(ps_sim* sim, double* acc_xy);
 
 /* Solver.updatePhysics (src/core.zig:245-268) called `frames` times = frames*sub_steps sub-steps. */
 int ps_step(ps_sim* sim, uint64_t frames);
+/* Solver.updatePhysics on HOST slices, as the reference runs it (src/core.zig:245, particles.positions / .velocities in
+ * host memory): upload pos_in + vel_in, `frames` x updatePhysics, write the new positions (and velocities) to pos_out
+ * (vel_out); either output may be NULL, outputs may alias inputs.  Same result as ps_upload + ps_step + ps_download.
+ * Integration-only scenes with pinned buffers (ps_host_alloc) are streamed in chunks so that the upload of one chunk,
+ * the kernels of another and the write-back of a third overlap (PCIe is full duplex). */
+int ps_frame_host(ps_sim* sim, const double* pos_in, const double* vel_in, double* pos_out, double* vel_out, uint64_t frames);
+int ps_frame_host_f32(ps_sim* sim, const float* pos_in, const float* vel_in, float* pos_out, float* vel_out, uint64_t frames);
 /* `substeps` iterations of the loop body at src/core.zig:247-267 (benchmarks count sub-steps). */
 int ps_step_substeps(ps_sim* sim, uint64_t substeps);
 /* Solver.toggle_acc (src/core.zig:239-241): flips gravity and the collision response mode. */

@@ -81,6 +81,8 @@ SYMBOLS = {
     "ps_spawn": (ctypes.c_int, [_P, _U64, ctypes.c_double, ctypes.c_double]),
     "ps_step": (ctypes.c_int, [_P, _U64]),
     "ps_step_substeps": (ctypes.c_int, [_P, _U64]),
+    "ps_frame_host": (ctypes.c_int, [_P, _P, _P, _P, _P, _U64]),
+    "ps_frame_host_f32": (ctypes.c_int, [_P, _P, _P, _P, _P, _U64]),
     "ps_toggle_acc": (ctypes.c_int, [_P]),
     "ps_set_acc": (ctypes.c_int, [_P, ctypes.c_int]),
     "ps_get_acc": (ctypes.c_int, [_P]),

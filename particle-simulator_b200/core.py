@@ -180,6 +180,11 @@ class Simulation:
     def step_substeps(self, substeps: int) -> None:
         _check(self._L.ps_step_substeps(self._h, substeps), self._h)
 
+    def frame_host(self, pos_in, vel_in, pos_out=None, vel_out=None, frames: int = 1) -> None:
+        """updatePhysics on host slices: upload, `frames` frames, write back (ps_frame_host[_f32])."""
+        fn = self._L.ps_frame_host if pos_in.dtype == np.float64 else self._L.ps_frame_host_f32
+        _check(fn(self._h, self._ptr(pos_in), self._ptr(vel_in), self._ptr(pos_out), self._ptr(vel_out), frames), self._h)
+
     def toggle_acc(self) -> None:
         _check(self._L.ps_toggle_acc(self._h), self._h)
 

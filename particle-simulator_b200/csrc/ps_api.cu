@@ -42,6 +42,7 @@ struct ps_sim {
     virtual int upload(const void* pos, const void* vel, bool host_f64) = 0;
     virtual int download(void* pos, void* vel, bool host_f64) = 0;
     virtual int step(uint64_t substeps) = 0;
+    virtual int frame_host(const void* pos_in, const void* vel_in, void* pos_out, void* vel_out, bool host_f64, uint64_t frames) = 0;
     virtual int device_state(void** px, void** py, void** vx, void** vy) = 0;
     virtual int contact_pairs(uint64_t* out, uint64_t cap, uint64_t* count) = 0;
     virtual int capture_pairs(bool on) = 0;
@@ -79,6 +80,8 @@ struct SimT final : ps_sim {
         col.destroy();
         cudaFree(px); cudaFree(py); cudaFree(vx); cudaFree(vy);
         cudaFree(stage);
+        for (int i = 0; i < kPipeStreams; ++i) { if (pipe[i]) cudaStreamDestroy(pipe[i]); if (pipe_done[i]) cudaEventDestroy(pipe_done[i]); }
+        if (pipe_go) cudaEventDestroy(pipe_go);
         if (own_stream) cudaStreamDestroy(own_stream);
     }
 
@@ -179,6 +182,78 @@ struct SimT final : ps_sim {
         }
         PS_CUDA_TRY(err, cudaStreamSynchronize(stream));
         return check_deferred();
+    }
+
+    // ---- host buffers in, one or more frames, host buffers out ------------------------------------------------
+    // Same result as upload + step + download.  When the scene is integration-only (particles independent) and
+    // the host buffers are pinned, the particles are cut into chunks that travel through a small pool of streams:
+    // while chunk i is written back to the host over PCIe, chunk i+1 is being read from it (the link is full
+    // duplex) and both overlap the integrate kernels of other chunks.
+    static constexpr int kPipeStreams = 4;
+    cudaStream_t pipe[kPipeStreams] = {};
+    cudaEvent_t pipe_done[kPipeStreams] = {}, pipe_go = nullptr;
+
+    template <class H>
+    int frame_host_pipelined(const H* pos_in, const H* vel_in, H* pos_out, H* vel_out, uint64_t frames) {
+        using HP = typename ps::Pair<H>::type;
+        void *a_pi = nullptr, *a_vi = nullptr, *a_po = nullptr, *a_vo = nullptr;
+        if (!ps::host_ptr_is_pinned(pos_in, &a_pi) || !ps::host_ptr_is_pinned(vel_in, &a_vi)) return -100;
+        if (pos_out && !ps::host_ptr_is_pinned(pos_out, &a_po)) return -100;
+        if (vel_out && !ps::host_ptr_is_pinned(vel_out, &a_vo)) return -100;
+        if (!pipe_go) {
+            for (int i = 0; i < kPipeStreams; ++i) {
+                PS_CUDA_TRY(err, cudaStreamCreateWithFlags(&pipe[i], cudaStreamNonBlocking));
+                PS_CUDA_TRY(err, cudaEventCreateWithFlags(&pipe_done[i], cudaEventDisableTiming));
+            }
+            PS_CUDA_TRY(err, cudaEventCreateWithFlags(&pipe_go, cudaEventDisableTiming));
+        }
+        const ps::StepConst<Real> k = ps::make_step_const<Real>(cfg, t_acc, rows, cols);
+        const uint64_t substeps = frames * cfg.sub_steps;
+        const uint64_t fuse = cfg.fuse_substeps > 1 ? cfg.fuse_substeps : 1;
+        const uint64_t chunk = 2ull << 20;                               // particles per chunk (multiple of 4)
+        PS_CUDA_TRY(err, cudaEventRecord(pipe_go, stream));
+        for (int i = 0; i < kPipeStreams; ++i) PS_CUDA_TRY(err, cudaStreamWaitEvent(pipe[i], pipe_go, 0));
+        const unsigned tg = 148 * 4;                                     // modest grids so that chunks of different streams co-run
+        int slot = 0;
+        for (uint64_t first = 0; first < n; first += chunk, slot = (slot + 1) % kPipeStreams) {
+            const uint64_t m = n - first < chunk ? n - first : chunk;
+            cudaStream_t st = pipe[slot];
+            ps::deinterleave_kernel<H, Real><<<tg, 256, 0, st>>>(reinterpret_cast<const HP*>(a_pi) + first, px + first, py + first, m);
+            ps::deinterleave_kernel<H, Real><<<tg, 256, 0, st>>>(reinterpret_cast<const HP*>(a_vi) + first, vx + first, vy + first, m);
+            launches += 2;
+            for (uint64_t left = substeps; left;) {
+                const uint64_t now = left < fuse ? left : fuse;
+                PS_CUDA_TRY(err, ps::launch_integrate_bounce<Real>(px + first, py + first, vx + first, vy + first, ps::round_up(m, 4), k, (int)now,
+                                                                   integrate_variant ? integrate_variant : 3, st));
+                ++launches;
+                left -= now;
+            }
+            if (a_po) { ps::interleave_kernel<Real, H><<<tg, 256, 0, st>>>(px + first, py + first, reinterpret_cast<HP*>(a_po) + first, m); ++launches; }
+            if (a_vo) { ps::interleave_kernel<Real, H><<<tg, 256, 0, st>>>(vx + first, vy + first, reinterpret_cast<HP*>(a_vo) + first, m); ++launches; }
+        }
+        PS_CUDA_TRY(err, cudaGetLastError());
+        for (int i = 0; i < kPipeStreams; ++i) {
+            PS_CUDA_TRY(err, cudaEventRecord(pipe_done[i], pipe[i]));
+            PS_CUDA_TRY(err, cudaStreamWaitEvent(stream, pipe_done[i], 0));
+        }
+        if (substeps) stepped_with_acc = t_acc;
+        substeps_done += substeps;
+        PS_CUDA_TRY(err, cudaStreamSynchronize(stream));                 // the caller owns its buffers again on return
+        return PS_OK;
+    }
+
+    int frame_host(const void* pos_in, const void* vel_in, void* pos_out, void* vel_out, bool host_f64, uint64_t frames) override {
+        DeviceGuard g(device);
+        if (!cfg.collisions && pos_in && vel_in && n >= (4ull << 20)) {
+            const int rc = host_f64 ? frame_host_pipelined((const double*)pos_in, (const double*)vel_in, (double*)pos_out, (double*)vel_out, frames)
+                                    : frame_host_pipelined((const float*)pos_in, (const float*)vel_in, (float*)pos_out, (float*)vel_out, frames);
+            if (rc != -100) return rc;                                   // -100: buffers not pinned, take the plain route
+        }
+        int rc = upload(pos_in, vel_in, host_f64);
+        if (rc != PS_OK) return rc;
+        rc = step(frames * cfg.sub_steps);
+        if (rc != PS_OK) return rc;
+        return download(pos_out, vel_out, host_f64);
     }
 
     int step(uint64_t substeps) override {
@@ -358,6 +433,12 @@ int ps_download_acc(ps_sim* s, double* acc_xy) {
 }
 
 int ps_step(ps_sim* s, uint64_t frames) { return s ? s->step(frames * s->cfg.sub_steps) : PS_ERR_BAD_ARG; }
+int ps_frame_host(ps_sim* s, const double* pos_in, const double* vel_in, double* pos_out, double* vel_out, uint64_t frames) {
+    return s ? s->frame_host(pos_in, vel_in, pos_out, vel_out, true, frames) : PS_ERR_BAD_ARG;
+}
+int ps_frame_host_f32(ps_sim* s, const float* pos_in, const float* vel_in, float* pos_out, float* vel_out, uint64_t frames) {
+    return s ? s->frame_host(pos_in, vel_in, pos_out, vel_out, false, frames) : PS_ERR_BAD_ARG;
+}
 int ps_step_substeps(ps_sim* s, uint64_t substeps) { return s ? s->step(substeps) : PS_ERR_BAD_ARG; }
 int ps_toggle_acc(ps_sim* s) { if (!s) return PS_ERR_BAD_ARG; s->t_acc = !s->t_acc; return PS_OK; }
 int ps_set_acc(ps_sim* s, int on) { if (!s) return PS_ERR_BAD_ARG; s->t_acc = on != 0; return PS_OK; }

@@ -212,3 +212,56 @@ def test_device_spawner_equals_host_generator(precision):
         got_p, got_v = sim.download(dtype=DTYPES[precision])
     assert_bit_exact(got_p, want_p, "positions")
     assert_bit_exact(got_v, want_v, "velocities")
+
+
+@pytest.mark.parametrize("precision", ["f32", "f64"])
+def test_frame_host_streamed_equals_upload_step_download(precision):
+    """ps_frame_host: updatePhysics on host slices.  With pinned buffers and an integration-only scene the particles are
+    streamed in chunks over several streams; the result must be what upload + step + download gives (and the oracle)."""
+    L = capi.load()
+    n = (9 << 20) + 13                      # > 4 chunks, ragged tail
+    scene = scenes.scaled_scene(n)
+    ptrs = [ctypes.c_void_p() for _ in range(4)]
+    for p in ptrs:
+        assert L.ps_host_alloc(ctypes.byref(p), n * 16) == capi.PS_OK
+    try:
+        arrs = [np.ctypeslib.as_array(ctypes.cast(p, ctypes.POINTER(ctypes.c_double)), shape=(n, 2)) for p in ptrs]
+        pos0, vel0 = scenes.spawn(scene, seed=3)
+        arrs[0][:] = pos0
+        arrs[1][:] = vel0
+        with Simulation(scene, precision=precision, collisions=False) as sim:
+            sim.set_acc(True)
+            sim.frame_host(arrs[0], arrs[1], arrs[2], arrs[3], frames=2)
+            streamed_p, streamed_v = arrs[2].copy(), arrs[3].copy()
+            dev_p, dev_v = sim.download()                      # the device state must agree with what was written back
+            assert sim.stats()["substeps_done"] == 16
+        with Simulation(scene, precision=precision, collisions=False) as sim:
+            sim.set_acc(True)
+            sim.upload(pos0, vel0)
+            sim.step(2)
+            plain_p, plain_v = sim.download()
+        assert_bit_exact(streamed_p, plain_p, "positions")
+        assert_bit_exact(streamed_v, plain_v, "velocities")
+        assert_bit_exact(dev_p, plain_p, "device positions")
+        assert_bit_exact(dev_v, plain_v, "device velocities")
+        rng = np.random.default_rng(1)
+        sample = np.sort(rng.choice(n, size=50_000, replace=False))
+        dt = DTYPES[precision]
+        want_p, want_v, _ = run_oracle(scene.with_(count=sample.size), pos0[sample].astype(dt), vel0[sample].astype(dt), 16,
+                                       collisions=False, t_acc=True)
+        assert_bit_exact(streamed_p[sample].astype(dt), want_p, "sampled positions vs oracle")
+        assert_bit_exact(streamed_v[sample].astype(dt), want_v, "sampled velocities vs oracle")
+    finally:
+        for p in ptrs:
+            L.ps_host_free(p)
+
+
+def test_frame_host_plain_route_with_collisions_and_pageable_buffers():
+    scene = scenes.default_scene()
+    pos0, vel0 = scenes.spawn(scene, seed=2)
+    want_p, want_v, _ = run_oracle(scene, pos0, vel0, 24, collisions=True)
+    out_p, out_v = np.empty_like(pos0), np.empty_like(vel0)
+    with Simulation(scene, collisions=True) as sim:
+        sim.frame_host(pos0, vel0, out_p, out_v, frames=3)
+    assert_bit_exact(out_p, want_p)
+    assert_bit_exact(out_v, want_v)
