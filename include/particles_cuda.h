@@ -111,6 +111,20 @@ int ps_spawn(ps_sim* sim, uint64_t seed, double vel_min, double vel_max);
 /* particles.accelerations (src/core.zig:16): a pure function of t_acc and g (:249-257). */
 int ps_download_acc(ps_sim* sim, double* acc_xy);
 
+/* ---- what main.zig does with the state after the step (no window on a headless box) ----------------------
+ * The draw loop's per-particle data (src/main.zig:102-107 -> src/gui.zig:83-86): SDL_FRect {x - r, y - r, 2r, 2r} in f32
+ * (positions and radius cast with @floatCast first), 4 floats per particle, index order. */
+int ps_export_rects(ps_sim* sim, float* rects_xywh);
+/* particles.colors (src/core.zig:17): r,g,b,a bytes per particle.  ps_rainbow_colors = Spawner.assignRainbowColors
+ * (src/core.zig:411-417) with colors.hsvToSdlColor (src/colors.zig:6-47) on the device. */
+int ps_set_colors(ps_sim* sim, const uint8_t* rgba);
+int ps_rainbow_colors(ps_sim* sim);
+int ps_get_colors(ps_sim* sim, uint8_t* rgba);
+/* A headless frame in place of the SDL window: width x height RGBA8, cleared to (0,0,0,0) (src/main.zig:100,141-146), every
+ * particle painted as a disc of its radius and colour in index order (later particles over earlier ones).  The reference blits
+ * an anti-aliased sprite (assets/circle.png); this rasteriser paints hard-edged discs (pixel centre inside the circle). */
+int ps_render(ps_sim* sim, uint32_t width, uint32_t height, uint8_t* rgba);
+
 /* ---- stepping ----------------------------------------------------------------------- */
 
 /* Solver.updatePhysics (src/core.zig:245-268) called `frames` times = frames*sub_steps sub-steps. */

@@ -79,6 +79,11 @@ SYMBOLS = {
     "ps_download_f32": (ctypes.c_int, [_P, _P, _P]),
     "ps_download_acc": (ctypes.c_int, [_P, _P]),
     "ps_spawn": (ctypes.c_int, [_P, _U64, ctypes.c_double, ctypes.c_double]),
+    "ps_export_rects": (ctypes.c_int, [_P, _P]),
+    "ps_set_colors": (ctypes.c_int, [_P, _P]),
+    "ps_rainbow_colors": (ctypes.c_int, [_P]),
+    "ps_get_colors": (ctypes.c_int, [_P, _P]),
+    "ps_render": (ctypes.c_int, [_P, ctypes.c_uint32, ctypes.c_uint32, _P]),
     "ps_step": (ctypes.c_int, [_P, _U64]),
     "ps_step_substeps": (ctypes.c_int, [_P, _U64]),
     "ps_frame_host": (ctypes.c_int, [_P, _P, _P, _P, _P, _U64]),

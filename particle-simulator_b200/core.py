@@ -167,6 +167,30 @@ class Simulation:
         vmax = self.scene.vel_max if vel_max is None else vel_max
         _check(self._L.ps_spawn(self._h, seed, vmin, vmax), self._h)
 
+    def export_rects(self) -> np.ndarray:
+        """(n, 4) float32 {x - r, y - r, 2r, 2r}: the draw loop's SDL_FRect per particle (src/main.zig:102-107)."""
+        out = np.empty((self.count, 4), dtype=np.float32)
+        _check(self._L.ps_export_rects(self._h, self._ptr(out)), self._h)
+        return out
+
+    def set_colors(self, rgba: np.ndarray) -> None:
+        assert rgba.dtype == np.uint8 and rgba.shape == (self.count, 4) and rgba.flags.c_contiguous
+        _check(self._L.ps_set_colors(self._h, self._ptr(rgba)), self._h)
+
+    def rainbow_colors(self) -> None:
+        _check(self._L.ps_rainbow_colors(self._h), self._h)
+
+    def get_colors(self) -> np.ndarray:
+        out = np.empty((self.count, 4), dtype=np.uint8)
+        _check(self._L.ps_get_colors(self._h, self._ptr(out)), self._h)
+        return out
+
+    def render(self, width: int, height: int) -> np.ndarray:
+        """Headless frame (height, width, 4) uint8 in place of the SDL window."""
+        out = np.empty((height, width, 4), dtype=np.uint8)
+        _check(self._L.ps_render(self._h, width, height, self._ptr(out)), self._h)
+        return out
+
     def download_acc(self, acc=None):
         if acc is None:
             acc = np.empty((self.count, 2), dtype=np.float64)

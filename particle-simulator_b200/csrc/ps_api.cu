@@ -15,6 +15,7 @@
 #include "ps_collide.cuh"
 #include "ps_common.cuh"
 #include "ps_integrate.cuh"
+#include "ps_render.cuh"
 #include "ps_slab.cuh"
 #include "ps_transfer.cuh"
 
@@ -51,6 +52,9 @@ struct ps_sim {
     virtual int check_deferred() = 0;
     virtual double dt() const = 0;
     virtual int spawn(uint64_t seed, double vmin, double vmax) = 0;
+    virtual int export_rects(float* rects) = 0;
+    virtual int colors_io(const uint8_t* in, uint8_t* out, bool rainbow) = 0;
+    virtual int render(uint32_t w, uint32_t h, uint8_t* rgba) = 0;
 
     int ensure_stage(uint64_t bytes) {
         if (bytes <= stage_bytes) return PS_OK;
@@ -80,6 +84,7 @@ struct SimT final : ps_sim {
         if (own_stream) cudaStreamSynchronize(own_stream);
         col.destroy();
         cudaFree(px); cudaFree(py); cudaFree(vx); cudaFree(vy);
+        cudaFree(colors); cudaFree(owner); cudaFree(image);
         cudaFree(stage);
         for (int i = 0; i < kPipeStreams; ++i) { if (pipe[i]) cudaStreamDestroy(pipe[i]); if (pipe_done[i]) cudaEventDestroy(pipe_done[i]); cudaFree(pipe_stage[i]); }
         if (pipe_go) cudaEventDestroy(pipe_go);
@@ -357,6 +362,66 @@ struct SimT final : ps_sim {
 
     double dt() const override { return (double)ps::make_step_const<Real>(cfg, false, rows, cols).dt; }
 
+    // ---- after the step: draw data and a headless frame (ps_render.cuh) -------------------------------------
+    uchar4* colors = nullptr;
+    uint32_t* owner = nullptr; uchar4* image = nullptr; uint64_t image_pixels = 0;
+
+    int ensure_colors() {
+        if (colors) return PS_OK;
+        PS_CUDA_TRY(err, cudaMalloc((void**)&colors, (n ? n : 1) * sizeof(uchar4)));
+        PS_CUDA_TRY(err, cudaMemsetAsync(colors, 0xff, (n ? n : 1) * sizeof(uchar4), stream));   // white until the caller sets them
+        return PS_OK;
+    }
+    int current_soa() {
+        if (cfg.collisions && n) return col.materialize_soa(px, py, vx, vy, stream, err, &launches);
+        return PS_OK;
+    }
+
+    int export_rects(float* rects) override {
+        DeviceGuard g(device);
+        if (n == 0) return PS_OK;
+        int rc = current_soa(); if (rc != PS_OK) return rc;
+        rc = ensure_stage(n * sizeof(float4)); if (rc != PS_OK) return rc;
+        ps::export_rects_kernel<Real><<<ps::transfer_grid(n), 256, 0, stream>>>(px, py, n, (float)cfg.radius, static_cast<float4*>(stage));
+        ++launches;
+        PS_CUDA_TRY(err, cudaMemcpyAsync(rects, stage, n * sizeof(float4), cudaMemcpyDeviceToHost, stream));
+        PS_CUDA_TRY(err, cudaStreamSynchronize(stream));
+        return PS_OK;
+    }
+
+    int colors_io(const uint8_t* in, uint8_t* out, bool rainbow) override {
+        DeviceGuard g(device);
+        int rc = ensure_colors(); if (rc != PS_OK) return rc;
+        if (n == 0) return PS_OK;
+        if (in) PS_CUDA_TRY(err, cudaMemcpyAsync(colors, in, n * sizeof(uchar4), cudaMemcpyHostToDevice, stream));
+        if (rainbow) { ps::rainbow_kernel<<<ps::transfer_grid(n), 256, 0, stream>>>(n, colors); ++launches; }
+        if (out) PS_CUDA_TRY(err, cudaMemcpyAsync(out, colors, n * sizeof(uchar4), cudaMemcpyDeviceToHost, stream));
+        PS_CUDA_TRY(err, cudaStreamSynchronize(stream));
+        return PS_OK;
+    }
+
+    int render(uint32_t w, uint32_t h, uint8_t* rgba) override {
+        DeviceGuard g(device);
+        const uint64_t pixels = (uint64_t)w * h;
+        if (!pixels || !rgba) return fail(PS_ERR_BAD_ARG, "ps_render: empty image");
+        if (n >= 0xffffffffull) return fail(PS_ERR_BAD_ARG, "ps_render: too many particles");
+        int rc = ensure_colors(); if (rc != PS_OK) return rc;
+        rc = current_soa(); if (rc != PS_OK) return rc;
+        if (pixels != image_pixels) {
+            cudaFree(owner); cudaFree(image); owner = nullptr; image = nullptr; image_pixels = 0;
+            PS_CUDA_TRY(err, cudaMalloc((void**)&owner, pixels * sizeof(uint32_t)));
+            PS_CUDA_TRY(err, cudaMalloc((void**)&image, pixels * sizeof(uchar4)));
+            image_pixels = pixels;
+        }
+        PS_CUDA_TRY(err, cudaMemsetAsync(owner, 0, pixels * sizeof(uint32_t), stream));
+        if (n) { ps::splat_owner_kernel<Real><<<ps::transfer_grid(n), 256, 0, stream>>>(px, py, n, (float)cfg.radius, w, h, owner); ++launches; }
+        ps::splat_resolve_kernel<<<ps::transfer_grid(pixels), 256, 0, stream>>>(owner, colors, pixels, image);
+        ++launches;
+        PS_CUDA_TRY(err, cudaMemcpyAsync(rgba, image, pixels * sizeof(uchar4), cudaMemcpyDeviceToHost, stream));
+        PS_CUDA_TRY(err, cudaStreamSynchronize(stream));
+        return PS_OK;
+    }
+
     int spawn(uint64_t seed, double vmin, double vmax) override {
         DeviceGuard g(device);
         if (n == 0) return PS_OK;
@@ -451,6 +516,12 @@ int ps_download(ps_sim* s, double* pos, double* vel) { return s ? s->download(po
 int ps_download_f32(ps_sim* s, float* pos, float* vel) { return s ? s->download(pos, vel, false) : PS_ERR_BAD_ARG; }
 
 int ps_spawn(ps_sim* s, uint64_t seed, double vel_min, double vel_max) { return s ? s->spawn(seed, vel_min, vel_max) : PS_ERR_BAD_ARG; }
+
+int ps_export_rects(ps_sim* s, float* rects_xywh) { return (s && (rects_xywh || !s->n)) ? s->export_rects(rects_xywh) : PS_ERR_BAD_ARG; }
+int ps_set_colors(ps_sim* s, const uint8_t* rgba) { return (s && rgba) ? s->colors_io(rgba, nullptr, false) : PS_ERR_BAD_ARG; }
+int ps_rainbow_colors(ps_sim* s) { return s ? s->colors_io(nullptr, nullptr, true) : PS_ERR_BAD_ARG; }
+int ps_get_colors(ps_sim* s, uint8_t* rgba) { return (s && rgba) ? s->colors_io(nullptr, rgba, false) : PS_ERR_BAD_ARG; }
+int ps_render(ps_sim* s, uint32_t width, uint32_t height, uint8_t* rgba) { return s ? s->render(width, height, rgba) : PS_ERR_BAD_ARG; }
 
 int ps_download_acc(ps_sim* s, double* acc_xy) {
     if (!s || !acc_xy) return PS_ERR_BAD_ARG;
