@@ -71,4 +71,4 @@ def test_headless_frame_matches_index_order_painter():
         img = sim.render(180, 120)
     want = splat_reference(pos, scene.radius, colors, 180, 120)
     assert np.array_equal(img, want)
-    assert img[..., 3].any() and not img[0, 0].any()      # something was drawn; the corner outside every disc stays clear
+    assert img[..., 3].any() and (img[..., 3] == 0).any()   # something was drawn, and some pixels stayed clear
