@@ -34,6 +34,9 @@
 #pragma once
 #include <cooperative_groups.h>
 
+#include <cstdio>
+#include <cstdlib>
+
 #include "ps_common.cuh"
 #include "ps_integrate.cuh"
 #include "ps_scan.cuh"
@@ -94,7 +97,12 @@ struct DevState {
     uint32_t pad;
     unsigned long long pairs_total, rounds_total;
     uint32_t dbg[4];           // first offending slot / cell when FLAG_CORRUPT is raised
+    uint32_t trace_on;         // PS_RESOLVE_TRACE: record the length and start time of every resolve round
+    uint32_t trace_rounds;
+    uint32_t trace_cnt[64];
+    uint32_t trace_ns[64];     // nanoseconds since the kernel's first round
 };
+__device__ __forceinline__ unsigned long long global_ns() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
 constexpr uint32_t FLAG_CELL_OVERFLOW = 1u, FLAG_CAPACITY = 2u, FLAG_CORRUPT = 4u;
 
 // contact-list entry: partner slot (28 bits) | offset index (3 bits) | role (1 = this particle is the centre)
@@ -493,7 +501,7 @@ __device__ __forceinline__ void resolve_pair(Rec<Real>& I, Rec<Real>& J, const S
 }
 
 constexpr int RESOLVE_THREADS = 256;
-constexpr uint32_t RESOLVE_TAIL = 2048;   // work lists this short are finished by one CTA with CTA barriers only
+constexpr uint32_t RESOLVE_TAIL = 512;    // work lists this short are finished by one CTA with CTA barriers only
 
 // One round over the work list `wl[0..cnt)`: every item {a, ea} is a particle whose head moved in the
 // previous round (or any particle with a list when r = 0) together with its head entry.  Appends the
@@ -512,6 +520,9 @@ __device__ __forceinline__ void resolve_round(Rec<Real>* rec, const uint32_t* __
             const uint2 item = __ldcg(wl + idx);
             const uint32_t a = item.x, ea = item.y;
             const uint32_t b = ea & ENT_SLOT_MASK;
+            // Round 0: every particle with a visible list is on the work list, and a pair can only be ready if the two
+            // heads name each other, in which case the lower slot's thread runs it.  So the higher slot need not look.
+            if (r == 0u && b < a) break;
             // everything that depends only on the item is requested at once (the records speculatively)
             const unsigned long long ha = __ldcg(head + a);
             const unsigned long long hb = __ldcg(head + b);
@@ -565,10 +576,13 @@ resolve_kernel(Rec<Real>* rec, const uint32_t* __restrict__ entries, unsigned lo
         return;
     }
     uint32_t r = r_start;                                    // > 0 only for the second phase of a slab sub-step (ps_slab.cuh)
+    const bool trace = leader && ds->trace_on && r_start == 0;
+    const unsigned long long t_begin = trace ? global_ns() : 0ull;
     // grid phase: long work lists, one grid barrier per round
     for (;; ++r) {
         const uint32_t cur = r % 3, nxt = (r + 1) % 3, nn = (r + 2) % 3;
         const uint32_t cnt = __ldcg(&ds->wl_count[cur]);
+        if (trace && r < 64) { ds->trace_cnt[r] = cnt; ds->trace_ns[r] = (uint32_t)(global_ns() - t_begin); }
         if (cnt <= RESOLVE_TAIL) break;                      // same value in every thread: the whole grid leaves together
         if (leader) ds->wl_count[nn] = 0;                    // consumed in round r-1, refilled in round r+1
         resolve_round<Real>(rec, entries, head, lists[cur], cnt, lists[nxt], &ds->wl_count[nxt], r,
@@ -580,6 +594,7 @@ resolve_kernel(Rec<Real>* rec, const uint32_t* __restrict__ entries, unsigned lo
     for (;; ++r) {
         const uint32_t cur = r % 3, nxt = (r + 1) % 3, nn = (r + 2) % 3;
         const uint32_t cnt = __ldcg(&ds->wl_count[cur]);
+        if (trace && r < 64) { ds->trace_cnt[r] = cnt; ds->trace_ns[r] = (uint32_t)(global_ns() - t_begin); }
         if (cnt == 0 || r + 2 >= HEAD_STAMP_MAX) break;
         __syncthreads();                                     // everyone has read cnt before the counters move on
         if (threadIdx.x == 0) ds->wl_count[nn] = 0;
@@ -591,6 +606,7 @@ resolve_kernel(Rec<Real>* rec, const uint32_t* __restrict__ entries, unsigned lo
     if (threadIdx.x == 0) {
         if (ds->wl_count[r % 3] != 0) atomicOr(&ds->flags, FLAG_CAPACITY);   // ran out of round stamps (never in practice)
         ds->rounds_last = r;
+        if (trace) ds->trace_rounds = r < 63 ? r + 1 : 64;
         ds->rounds_total += r - r_start;
         if (r_start == 0) {
             ds->inc_total = ds->entries_used;
@@ -653,6 +669,7 @@ struct Collider {
         for (int i = 0; i < 3; ++i) if ((rc = alloc(&wl[i], n, err))) return rc;
         if ((rc = alloc(&ds, 1, err))) return rc;
         PS_CUDA_TRY(err, cudaMemsetAsync(ds, 0, sizeof(DevState), st));
+        if (getenv("PS_RESOLVE_TRACE")) { const uint32_t one = 1; PS_CUDA_TRY(err, cudaMemcpyAsync(&ds->trace_on, &one, sizeof(one), cudaMemcpyHostToDevice, st)); }
         int per_sm = 0, sms = 0;
         PS_CUDA_TRY(err, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, resolve_kernel<Real>, RESOLVE_THREADS, 0));
         PS_CUDA_TRY(err, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
@@ -759,6 +776,11 @@ struct Collider {
         DevState h{};
         PS_CUDA_TRY(err, cudaMemcpyAsync(&h, ds, sizeof(DevState), cudaMemcpyDeviceToHost, st));
         PS_CUDA_TRY(err, cudaStreamSynchronize(st));
+        if (h.trace_on) {                                    // PS_RESOLVE_TRACE: rounds of the last sub-step to stderr
+            std::string line = "[resolve trace] round:items@us";
+            for (uint32_t i = 0; i < h.trace_rounds; ++i) line += " " + std::to_string(i) + ":" + std::to_string(h.trace_cnt[i]) + "@" + std::to_string(h.trace_ns[i] / 1000);
+            fprintf(stderr, "%s\n", line.c_str());
+        }
         out->pairs_last = h.inc_total / 2;
         out->pairs_total = h.pairs_total;
         out->rounds_last = h.rounds_last;
