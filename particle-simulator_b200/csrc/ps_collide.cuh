@@ -109,11 +109,18 @@ constexpr uint32_t FLAG_CELL_OVERFLOW = 1u, FLAG_CAPACITY = 2u, FLAG_CORRUPT = 4
 constexpr uint32_t ENT_SLOT_MASK = (1u << 28) - 1;
 __device__ __forceinline__ uint32_t make_entry(uint32_t partner, uint32_t o, uint32_t centre) { return partner | (o << 28) | (centre << 31); }
 
+// x / grid_size (src/core.zig:104-105).  When grid_size is a power of two (the reference's 4.0) the quotient equals
+// x * (1 / grid_size) bit for bit (scaling by a power of two is exact), which spares the IEEE division sequence.
+template <class Real>
+__device__ __forceinline__ Real cell_coord(Real x, const StepConst<Real>& k) {
+    return k.gs_pow2 ? x * k.inv_gs : div_rn(x, k.grid_size);
+}
+
 // computeCoordinate + computeGridIndex (src/core.zig:103-121)
 template <class Real>
 __device__ __forceinline__ uint32_t cell_of(Real x, Real y, const StepConst<Real>& k) {
-    const Real fi = floor_r(div_rn(x, k.grid_size));
-    const Real fj = floor_r(div_rn(y, k.grid_size));
+    const Real fi = floor_r(cell_coord<Real>(x, k));
+    const Real fj = floor_r(cell_coord<Real>(y, k));
     // positions are inside [r, dim-r] here; the clamp mirrors @min(i, cols-1) and guards NaN / negatives
     uint32_t i = fi > (Real)0 ? (fi < (Real)k.cols ? (uint32_t)fi : k.cols - 1) : 0u;
     uint32_t j = fj > (Real)0 ? (fj < (Real)k.rows ? (uint32_t)fj : k.rows - 1) : 0u;
@@ -302,9 +309,92 @@ struct SlabView {
     uint32_t* brem;           // per slot: sub-list length of a blocked particle
 };
 
-__device__ __forceinline__ unsigned long long range_bits(unsigned long long mask, uint32_t off, uint32_t len) {
-    if (len == 0u) return 0ull;
-    return (mask >> off) & (len >= 64u ? ~0ull : ((1ull << len) - 1ull));
+// Bit-mask helpers for the candidate masks: 32-bit when the 3x3 block holds at most 32 candidates (the usual case:
+// ~4 at the reference density), 64-bit up to 64, the generic two-walk path beyond.
+template <class M> struct MaskBits;
+template <> struct MaskBits<uint32_t> {
+    static constexpr uint32_t W = 32;
+    static __device__ __forceinline__ uint32_t range(uint32_t m, uint32_t off, uint32_t len) { return len ? ((m >> off) & (len >= 32u ? ~0u : ((1u << len) - 1u))) : 0u; }
+    static __device__ __forceinline__ uint32_t popc(uint32_t m) { return (uint32_t)__popc(m); }
+    static __device__ __forceinline__ uint32_t first(uint32_t m) { return (uint32_t)__ffs((int)m) - 1u; }
+    static __device__ __forceinline__ uint32_t one(uint32_t bit) { return 1u << bit; }
+};
+template <> struct MaskBits<unsigned long long> {
+    static constexpr uint32_t W = 64;
+    static __device__ __forceinline__ unsigned long long range(unsigned long long m, uint32_t off, uint32_t len) { return len ? ((m >> off) & (len >= 64u ? ~0ull : ((1ull << len) - 1ull))) : 0ull; }
+    static __device__ __forceinline__ uint32_t popc(unsigned long long m) { return (uint32_t)__popcll(m); }
+    static __device__ __forceinline__ uint32_t first(unsigned long long m) { return (uint32_t)__ffsll((long long)m) - 1u; }
+    static __device__ __forceinline__ unsigned long long one(uint32_t bit) { return 1ull << bit; }
+};
+
+struct OwnFlags { bool a_own, l_own, r_own; };   // which columns of the 3x3 block belong to this rank (all true on one GPU)
+
+// checkCollision (:339-346) for every candidate of the three column ranges, once: (xj-xi)^2 does not depend on which
+// of the two is i, so one test serves both roles.  Bit offset of slot q: left column q - l0, own column nL + q - m0,
+// right column nL + nM + q - r0.
+template <class Real, class M>
+__device__ __forceinline__ M test_block(const Rec<Real>* __restrict__ rec, uint32_t a, decltype(ld_pos((const Rec<Real>*)nullptr)) pa,
+                                        const Stencil& st, Real r2sq) {
+    M mask = 0;
+    uint32_t bit = 0;
+    auto test = [&](uint32_t b, uint32_t e) {
+        for (uint32_t q = b; q < e; ++q, ++bit) {
+            const auto pq = ld_pos(rec + q);
+            const Real dx = pq.x - pa.x, dy = pq.y - pa.y;
+            const Real d2 = dx * dx + dy * dy;
+            if (d2 < r2sq && q != a) mask |= MaskBits<M>::one(bit);
+        }
+    };
+    if (st.left) test(st.l0, st.l3);
+    test(st.m0, st.m3);
+    if (st.right) test(st.r0, st.r3);
+    return mask;
+}
+
+// number of entries in a's sub-list; own-cell partners appear twice (a as neighbour and a as centre, Q1)
+template <class M, bool SLAB>
+__device__ __forceinline__ uint32_t count_block(M mask, const Stencil& st, uint32_t nL, uint32_t nM, OwnFlags f) {
+    using B = MaskBits<M>;
+    if (!SLAB || (f.a_own && f.l_own && f.r_own))            // every column of the block is an own column: nothing to filter
+        return B::popc(mask) + B::popc(B::range(mask, nL + (st.m1 - st.m0), st.m2 - st.m1));
+    uint32_t cnt = 0;
+    if (f.l_own) cnt += B::popc(B::range(mask, 0u, st.l2 - st.l0));                        // a neighbour of left-column centres
+    if (f.r_own) cnt += B::popc(B::range(mask, nL + nM, st.r1 - st.r0));                   // ... of right-column centres
+    if (f.a_own) cnt += B::popc(B::range(mask, nL, nM))                                    // own column, both roles
+                      + B::popc(B::range(mask, nL + (st.m1 - st.m0), st.m2 - st.m1))       // own cell listed twice
+                      + B::popc(B::range(mask, nL + nM + (st.r1 - st.r0), st.r3 - st.r1))  // a centre, right column
+                      + B::popc(B::range(mask, st.l2 - st.l0, st.l3 - st.l2));             // a centre, (-1,1)
+    return cnt;
+}
+
+// replay the mask in the reference's list order (the eleven segments documented at walk_contacts)
+template <class M>
+__device__ __forceinline__ uint32_t emit_block(M mask, const Stencil& st, uint32_t a, uint32_t nL, uint32_t nM, OwnFlags f,
+                                               uint32_t* __restrict__ entries, uint32_t w) {
+    using B = MaskBits<M>;
+    auto emit = [&](uint32_t b, uint32_t e, uint32_t off, uint32_t o, uint32_t centre) {
+        if (e <= b) return;
+        M bits = B::range(mask, off, e - b);
+        while (bits) {
+            const uint32_t j = B::first(bits);
+            bits &= bits - 1;
+            entries[w++] = make_entry(b + j, o, centre);
+        }
+    };
+    const uint32_t oM = nL - st.m0, oR = nL + nM - st.r0;                // wrap-around arithmetic: offset = oX + q
+    if (st.left && f.l_own) { emit(st.l0, st.l1, 0u, 3u, 0u); emit(st.l1, st.l2, st.l1 - st.l0, 2u, 0u); }
+    if (f.a_own) {
+        emit(st.m0, st.m1, oM + st.m0, 1u, 0u);
+        emit(st.m1, a, oM + st.m1, 0u, 0u);
+        emit(st.m1, a, oM + st.m1, 0u, 1u);
+        emit(a + 1, st.m2, oM + a + 1, 0u, 1u);
+        emit(st.m2, st.m3, oM + st.m2, 1u, 1u);
+        if (st.right) { emit(st.r1, st.r2, oR + st.r1, 2u, 1u); emit(st.r2, st.r3, oR + st.r2, 3u, 1u); }
+        if (st.left) emit(st.l2, st.l3, st.l2 - st.l0, 4u, 1u);
+        emit(a + 1, st.m2, oM + a + 1, 0u, 0u);
+    }
+    if (st.right && f.r_own) emit(st.r0, st.r1, oR + st.r0, 4u, 0u);
+    return w;
 }
 
 template <class Real, bool SLAB>
@@ -316,7 +406,7 @@ detect_kernel(const Rec<Real>* __restrict__ rec, const uint32_t* __restrict__ ce
     const uint32_t a = blockIdx.x * blockDim.x + threadIdx.x;
     // SLAB: `n` is the record capacity on entry; the slot count lives on the device.  The slot's position is
     // requested before that count is known (any slot below the capacity may be read), so the two loads overlap.
-    const auto pa_early = a < n ? ld_pos(rec + a) : decltype(ld_pos(rec)){};
+    const auto pa = a < n ? ld_pos(rec + a) : decltype(ld_pos(rec)){};
     if (SLAB) n = *sv.n_local;
     const bool valid = a < n;
     if (ds->flags) {                                         // error state (uniform: set by an earlier launch): no lists, no resolve
@@ -324,15 +414,17 @@ detect_kernel(const Rec<Real>* __restrict__ rec, const uint32_t* __restrict__ ce
         return;
     }
     Stencil st{};
-    uint32_t cnt = 0, nL = 0, nM = 0, nR = 0;
-    unsigned long long mask = 0ull;
-    bool wide = false, a_own = true, l_own = true, r_own = true, blocked = false;
+    uint32_t cnt = 0, nL = 0, nM = 0;
+    uint32_t m32 = 0u;
+    unsigned long long m64 = 0ull;
+    int path = 0;                                            // 0: 32-bit mask, 1: 64-bit mask, 2: generic walk
+    OwnFlags own{true, true, true};
+    bool blocked = false;
     if (valid) {
-        const auto pa = pa_early;
         uint32_t c;
         if (SLAB) {
             // local cell: global computeCoordinate, then shift by the slab's first local column
-            const Real fi = floor_r(div_rn(pa.x, k.grid_size)), fj = floor_r(div_rn(pa.y, k.grid_size));
+            const Real fi = floor_r(cell_coord<Real>(pa.x, k)), fj = floor_r(cell_coord<Real>(pa.y, k));
             const uint32_t gi = fi > (Real)0 ? (fi < (Real)sv.gcols ? (uint32_t)fi : sv.gcols - 1) : 0u;
             const uint32_t gj = fj > (Real)0 ? (fj < (Real)k.rows ? (uint32_t)fj : k.rows - 1) : 0u;
             const uint32_t lx = gi - sv.col_off;
@@ -341,9 +433,9 @@ detect_kernel(const Rec<Real>* __restrict__ rec, const uint32_t* __restrict__ ce
                 if (!atomicOr(&ds->flags, FLAG_CORRUPT)) { ds->dbg[0] = a; ds->dbg[1] = gi; ds->dbg[2] = gj; ds->dbg[3] = n; }
                 c = 0;
             }
-            a_own = lx >= sv.gl && lx < sv.ncl - sv.gr;
-            l_own = lx >= 1u && (lx - 1u) >= sv.gl && (lx - 1u) < sv.ncl - sv.gr;
-            r_own = (lx + 1u) >= sv.gl && (lx + 1u) < sv.ncl - sv.gr;
+            own.a_own = lx >= sv.gl && lx < sv.ncl - sv.gr;
+            own.l_own = lx >= 1u && (lx - 1u) >= sv.gl && (lx - 1u) < sv.ncl - sv.gr;
+            own.r_own = (lx + 1u) >= sv.gl && (lx + 1u) < sv.ncl - sv.gr;
             blocked = a < *sv.n_blocked;
         } else {
             c = cell_of<Real>(pa.x, pa.y, k);
@@ -351,37 +443,18 @@ detect_kernel(const Rec<Real>* __restrict__ rec, const uint32_t* __restrict__ ce
         st = load_stencil<Real>(cell_start, c, k);
         nL = st.left ? st.l3 - st.l0 : 0u;
         nM = st.m3 - st.m0;
-        nR = st.right ? st.r3 - st.r0 : 0u;
-        wide = nL + nM + nR > 64u;
-        if (!wide) {
-            // checkCollision (:339-346); (xj-xi)^2 does not depend on which of the two is i, so one test serves both roles
-            const Real r2sq = k.r2sq;
-            uint32_t bit = 0;
-            auto test = [&](uint32_t b, uint32_t e) {
-                for (uint32_t q = b; q < e; ++q, ++bit) {
-                    const auto pq = ld_pos(rec + q);
-                    const Real dx = pq.x - pa.x, dy = pq.y - pa.y;
-                    const Real d2 = dx * dx + dy * dy;
-                    if (d2 < r2sq && q != a) mask |= 1ull << bit;
-                }
-            };
-            if (st.left) test(st.l0, st.l3);
-            test(st.m0, st.m3);
-            if (st.right) test(st.r0, st.r3);
-            // own-cell partners appear twice in a's sub-list (a as neighbour and a as centre, Q1)
-            if (!SLAB || (a_own && l_own && r_own)) {            // every column of the block is an own column: nothing to filter
-                cnt = (uint32_t)__popcll(mask) + (uint32_t)__popcll(range_bits(mask, nL + (st.m1 - st.m0), st.m2 - st.m1));
-            } else {
-                if (l_own) cnt += (uint32_t)__popcll(range_bits(mask, 0u, st.l2 - st.l0));                       // a neighbour of left-column centres
-                if (r_own) cnt += (uint32_t)__popcll(range_bits(mask, nL + nM, st.r1 - st.r0));                  // ... of right-column centres
-                if (a_own) cnt += (uint32_t)__popcll(range_bits(mask, nL, nM))                                    // own column, both roles
-                                + (uint32_t)__popcll(range_bits(mask, nL + (st.m1 - st.m0), st.m2 - st.m1))       // own cell listed twice
-                                + (uint32_t)__popcll(range_bits(mask, nL + nM + (st.r1 - st.r0), st.r3 - st.r1))  // a centre, right column
-                                + (uint32_t)__popcll(range_bits(mask, st.l2 - st.l0, st.l3 - st.l2));             // a centre, (-1,1)
-            }
+        const uint32_t nR = st.right ? st.r3 - st.r0 : 0u;
+        const uint32_t total = nL + nM + nR;
+        path = total <= 32u ? 0 : (total <= 64u ? 1 : 2);
+        if (path == 0) {
+            m32 = test_block<Real, uint32_t>(rec, a, pa, st, k.r2sq);
+            cnt = count_block<uint32_t, SLAB>(m32, st, nL, nM, own);
+        } else if (path == 1) {
+            m64 = test_block<Real, unsigned long long>(rec, a, pa, st, k.r2sq);
+            cnt = count_block<unsigned long long, SLAB>(m64, st, nL, nM, own);
         } else {
             walk_contacts<Real>(a, rec, st, k.r2sq, [&](uint32_t, uint32_t o, uint32_t centre) {
-                const bool keep = !SLAB || (centre ? a_own : (o >= 2u && o <= 3u ? l_own : (o == 4u ? r_own : a_own)));
+                const bool keep = !SLAB || (centre ? own.a_own : (o >= 2u && o <= 3u ? own.l_own : (o == 4u ? own.r_own : own.a_own)));
                 cnt += keep ? 1u : 0u;
             });
         }
@@ -407,34 +480,14 @@ detect_kernel(const Rec<Real>* __restrict__ rec, const uint32_t* __restrict__ ce
     head[a] = head_word(0u, blocked ? 0u : cnt, begin);
     if (SLAB && blocked) sv.brem[a] = cnt;                   // brem is zero everywhere else (cleared at creation and by the unblock kernel)
     if (!cnt) return;
-    uint32_t w = begin;
-    if (!wide) {
-        // replay the mask in list order; bit offset of slot q: left column q - l0, own column nL + q - m0, right column nL + nM + q - r0
-        auto emit = [&](uint32_t b, uint32_t e, uint32_t off, uint32_t o, uint32_t centre) {
-            if (e <= b) return;
-            unsigned long long bits = range_bits(mask, off, e - b);
-            while (bits) {
-                const uint32_t j = (uint32_t)__ffsll((long long)bits) - 1u;
-                bits &= bits - 1ull;
-                entries[w++] = make_entry(b + j, o, centre);
-            }
-        };
-        const uint32_t oM = nL - st.m0, oR = nL + nM - st.r0;          // wrap-around arithmetic: offset = oX + q
-        if (st.left && l_own) { emit(st.l0, st.l1, 0u, 3u, 0u); emit(st.l1, st.l2, st.l1 - st.l0, 2u, 0u); }
-        if (a_own) {
-            emit(st.m0, st.m1, oM + st.m0, 1u, 0u);
-            emit(st.m1, a, oM + st.m1, 0u, 0u);
-            emit(st.m1, a, oM + st.m1, 0u, 1u);
-            emit(a + 1, st.m2, oM + a + 1, 0u, 1u);
-            emit(st.m2, st.m3, oM + st.m2, 1u, 1u);
-            if (st.right) { emit(st.r1, st.r2, oR + st.r1, 2u, 1u); emit(st.r2, st.r3, oR + st.r2, 3u, 1u); }
-            if (st.left) emit(st.l2, st.l3, st.l2 - st.l0, 4u, 1u);
-            emit(a + 1, st.m2, oM + a + 1, 0u, 0u);
-        }
-        if (st.right && r_own) emit(st.r0, st.r1, oR + st.r0, 4u, 0u);
+    if (path == 0) {
+        emit_block<uint32_t>(m32, st, a, nL, nM, own, entries, begin);
+    } else if (path == 1) {
+        emit_block<unsigned long long>(m64, st, a, nL, nM, own, entries, begin);
     } else {
+        uint32_t w = begin;
         walk_contacts<Real>(a, rec, st, k.r2sq, [&](uint32_t q, uint32_t o, uint32_t centre) {
-            const bool keep = !SLAB || (centre ? a_own : (o >= 2u && o <= 3u ? l_own : (o == 4u ? r_own : a_own)));
+            const bool keep = !SLAB || (centre ? own.a_own : (o >= 2u && o <= 3u ? own.l_own : (o == 4u ? own.r_own : own.a_own)));
             if (keep) entries[w++] = make_entry(q, o, centre);
         });
     }

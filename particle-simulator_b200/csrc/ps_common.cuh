@@ -2,6 +2,7 @@
 #pragma once
 #include <cuda_runtime.h>
 
+#include <cmath>
 #include <cstdint>
 #include <cstdio>
 #include <string>
@@ -28,6 +29,8 @@ struct StepConst {
     Real min_dis;     // 2.0 * radius                                :372
     Real k_coef;      // -(1.0 + particle_damping)                   :368
     Real grid_size;   // SpatialHashGrid.grid_size                   :75
+    Real inv_gs;      // 1 / grid_size, used only when grid_size is a power of two (then x * inv_gs == x / grid_size exactly)
+    int gs_pow2;
     uint32_t rows, cols;
     int t_acc;
 };
@@ -56,6 +59,12 @@ inline StepConst<Real> make_step_const(const ps_config& c, bool t_acc, uint32_t 
     k.min_dis = r2;
     k.k_coef = -((Real)1.0 + (Real)c.particle_damping);
     k.grid_size = (Real)c.grid_size;
+    {
+        int e = 0;
+        const double m = std::frexp((double)k.grid_size, &e);       // grid_size = m * 2^e, m in [0.5, 1)
+        k.gs_pow2 = (k.grid_size > (Real)0 && m == 0.5 && e > -100 && e < 100) ? 1 : 0;
+        k.inv_gs = k.gs_pow2 ? (Real)std::ldexp(1.0, 1 - e) : (Real)0;
+    }
     k.rows = rows; k.cols = cols;
     k.t_acc = t_acc ? 1 : 0;
     return k;

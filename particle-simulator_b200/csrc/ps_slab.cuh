@@ -73,7 +73,7 @@ template <class Real> __device__ __forceinline__ uint32_t* halo_pids(void* buf, 
 
 template <class Real>
 __device__ __forceinline__ void global_cell(Real x, Real y, const StepConst<Real>& k, uint32_t gcols, uint32_t& gi, uint32_t& gj) {
-    const Real fi = floor_r(div_rn(x, k.grid_size)), fj = floor_r(div_rn(y, k.grid_size));   // computeCoordinate, src/core.zig:103-115
+    const Real fi = floor_r(cell_coord<Real>(x, k)), fj = floor_r(cell_coord<Real>(y, k));   // computeCoordinate, src/core.zig:103-115
     gi = fi > (Real)0 ? (fi < (Real)gcols ? (uint32_t)fi : gcols - 1) : 0u;
     gj = fj > (Real)0 ? (fj < (Real)k.rows ? (uint32_t)fj : k.rows - 1) : 0u;
 }
@@ -118,7 +118,7 @@ slab_spawn_kernel(uint64_t n_total, uint64_t seed_base, double radius, double wi
     for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_total; i += stride) {
         const double x = radius + (width - radius) * uniform01_dev(seed_base, i, 0);
         const Real rx = (Real)x;
-        const Real fi = floor_r(div_rn(rx, k.grid_size));
+        const Real fi = floor_r(cell_coord<Real>(rx, k));
         const uint32_t gi = fi > (Real)0 ? (fi < (Real)g.gcols ? (uint32_t)fi : g.gcols - 1) : 0u;
         if (gi < g.x0 || gi >= g.x1) continue;
         const double y = radius + (height - radius) * uniform01_dev(seed_base, i, 1);

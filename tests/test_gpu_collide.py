@@ -168,3 +168,13 @@ def test_api_mirror_reads_like_main_zig():
     assert_bit_exact(particles.velocities, v)
     assert particles.accelerations[0].tolist() == [0.0, 50.0]
     particles.deinit()
+
+
+@pytest.mark.parametrize("precision", ["f64", "f32"])
+@pytest.mark.parametrize("radius,grid_size", [(2.5, 5.0), (3.0, 6.0), (2.0, 4.7)])
+def test_grid_size_not_a_power_of_two(precision, radius, grid_size):
+    """x / grid_size takes the IEEE division path when grid_size is not a power of two; 4.7 also exercises the
+    reference's quirk that rows/cols come from the TRUNCATED grid size while the cell index uses the exact one
+    (src/core.zig:61-67 vs :104-105), so the last column and row absorb the clamp."""
+    scene = scenes.Scene(count=3000, radius=radius, width=400.0, height=300.0, grid_size=grid_size)
+    check(scene, 9, 80, precision, False, contacts_per_particle=48)
