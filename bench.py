@@ -485,11 +485,20 @@ def run_collide(args):
 
 def main():
     args = parse_args()
-    if args.impl == "reference":
-        return run_reference(args)
-    if args.workload == "collide":
-        return run_collide(args)
-    return run_ours(args)
+    # The contract is ONE JSON line on stdout.  Libraries loaded later write there too (NCCL prints its version banner
+    # to fd 1), so everything else is sent to stderr and only the JSON line goes to the real stdout.
+    sys.stdout.flush()
+    real_stdout = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    sys.stdout = real_stdout
+    try:
+        if args.impl == "reference":
+            return run_reference(args)
+        if args.workload == "collide":
+            return run_collide(args)
+        return run_ours(args)
+    finally:
+        real_stdout.flush()
 
 
 if __name__ == "__main__":
