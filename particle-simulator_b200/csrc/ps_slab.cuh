@@ -380,6 +380,8 @@ struct SlabCollider {
     int fail(int status, const std::string& text) { err.status = status; err.text = text; return status; }
     // PS_SLAB_DEBUG=1: synchronise after every stage kernel and name the one that faulted
     bool debug_sync = getenv("PS_SLAB_DEBUG") != nullptr;
+    bool force_late = getenv("PS_SLAB_FORCE_LATE") != nullptr;
+    uint64_t late_sends = 0;       // sub-steps in which M1 had to wait for phase B
     int dbg(const char* what) {
         if (!debug_sync) return PS_OK;
         const cudaError_t e = cudaStreamSynchronize(stream);
@@ -651,7 +653,9 @@ struct SlabCollider {
         if ((rc = read_back())) return rc;                                        // the one host synchronisation of the sub-step
         h_step = hc->sd;
         r0_step = hc->ds.rounds_last + 1;
-        send_now_step = g.gr && !h_step.right_incomplete;
+        // PS_SLAB_FORCE_LATE=1 (tests): behave as if the right boundary always depended on the left one
+        send_now_step = g.gr && !h_step.right_incomplete && !force_late;
+        if (g.gr && !send_now_step) ++late_sends;
         return PS_OK;
     }
 

@@ -105,7 +105,9 @@ def _two_rank_worker(rank, world, port, tmpdir, case):
     if rank == 0:
         idt = torch.frombuffer(bytearray(SlabSimulation.unique_id()), dtype=torch.uint8).clone()
     dist.broadcast(idt, 0)
-    scene, seed, substeps, precision, t_acc = case
+    scene, seed, substeps, precision, t_acc = case[:5]
+    if len(case) > 5 and case[5]:
+        os.environ["PS_SLAB_FORCE_LATE"] = "1"      # every rank sends its boundary states only after its own phase B
     pos0, vel0 = scenes.spawn(scene, seed=seed)
     with SlabSimulation(scene, rank, world, bytes(idt.numpy().tobytes()), precision=precision, device=rank, contacts_per_particle=32) as s:
         s.upload_global(pos0, vel0)
@@ -124,6 +126,7 @@ CASES = {
     "default_f32_gravity": (scenes.default_scene(), 2, 400, "f32", True),
     "dense_narrow": (scenes.Scene(count=3000, width=64.0, height=400.0), 3, 150, "f64", False),   # 16 columns: 8 per rank
     "one_million": (scenes.scaled_scene(1 << 20), 1, 24, "f32", False),
+    "late_boundary_path": (scenes.default_scene(), 5, 120, "f64", True, True),
 }
 
 
@@ -136,7 +139,7 @@ def test_two_ranks_equal_oracle(name, world, tmp_path):
     if torch.cuda.device_count() < world:
         pytest.skip(f"needs {world} GPUs")
     case = CASES[name]
-    scene, seed, substeps, precision, t_acc = case
+    scene, seed, substeps, precision, t_acc = case[:5]
     dtype = np.float64 if precision == "f64" else np.float32
     port = 29600 + (os.getpid() % 1000)
     mp.spawn(_two_rank_worker, args=(world, port, str(tmp_path), case), nprocs=world, join=True)
