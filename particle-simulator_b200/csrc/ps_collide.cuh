@@ -398,7 +398,7 @@ __device__ __forceinline__ uint32_t emit_block(M mask, const Stencil& st, uint32
 }
 
 template <class Real, bool SLAB>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, sizeof(Real) == 4 ? 6 : 4)   // 40 / 64 registers: more resident warps to hide the load latency
 detect_kernel(const Rec<Real>* __restrict__ rec, const uint32_t* __restrict__ cell_start, uint32_t n, StepConst<Real> k,
               uint32_t* __restrict__ entries, uint32_t entries_cap, unsigned long long* __restrict__ head,
               uint2* __restrict__ wl0, DevState* __restrict__ ds, SlabView sv) {
