@@ -167,7 +167,7 @@ bin_kernel(const Rec<Real>* __restrict__ rec_old, uint32_t n, StepConst<Real> k,
     Rec<Real> r = ld_rec(rec_old + s);
     integrate_rec<Real>(r, k);
     const uint32_t c = cell_of<Real>(r.x, r.y, k);
-    const uint32_t a = atomicAdd(cell_count + c, 1u);           // grid_array[c] += 1   src/core.zig:132
+    const uint32_t a = cell_count_fetch_inc(cell_count, c);     // grid_array[c] += 1   src/core.zig:132 (u8 counters, :51)
     slot_cell[s] = c;
     arrival[s] = a;
     if (a >= 255u) atomicOr(&ds->flags, FLAG_CELL_OVERFLOW);    // the reference's u8 would wrap here
@@ -179,7 +179,8 @@ place_kernel(const uint32_t* __restrict__ slot_cell, const uint32_t* __restrict_
              const uint32_t* __restrict__ cell_start, uint32_t n, uint32_t* __restrict__ tmp_id) {
     const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= n) return;
-    tmp_id[cell_start[slot_cell[s]] + arrival[s]] = pid_old[s];
+    const uint32_t dst = cell_start[slot_cell[s]] + arrival[s];
+    if (dst < n) tmp_id[dst] = pid_old[s];                      // out of range only after a flagged counter overflow
 }
 
 template <class Real>
@@ -198,9 +199,10 @@ move_kernel(const Rec<Real>* __restrict__ rec_old, const uint32_t* __restrict__ 
     const uint32_t c = slot_cell[s];
     const uint32_t b = cell_start[c], e = cell_start[c + 1];
     uint32_t rank = 0;
-    for (uint32_t t = b; t < e; ++t) rank += tmp_id[t] < id ? 1u : 0u;   // ascending index inside the cell, src/core.zig:146-158
+    for (uint32_t t = b; t < e && t < n; ++t) rank += tmp_id[t] < id ? 1u : 0u;   // ascending index inside the cell, src/core.zig:146-158
     Rec<Real> r = ld_rec(rec_old + s);
     integrate_rec<Real>(r, k);                                            // same arithmetic as bin_kernel, bit for bit
+    if (b + rank >= n) return;                                            // only after a flagged counter overflow
     st_rec(rec_new + b + rank, r);
     pid_new[b + rank] = id;
 }
@@ -707,7 +709,7 @@ struct Collider {
         pairs_cap = entries_cap / 2;
         const uint64_t scan_len = (uint64_t)ncell > n ? ncell : n;
         int rc;
-        if ((rc = alloc(&cell_count, (uint64_t)ncell, err))) return rc;
+        if ((rc = alloc(&cell_count, cell_count_bytes(ncell) / 4, err))) return rc;
         if ((rc = alloc(&cell_start, (uint64_t)ncell + 3, err))) return rc;
         if ((rc = alloc(&scan_sums, scan_tiles(scan_len) + 1, err))) return rc;
         if ((rc = alloc(&slot_cell, n, err))) return rc;
@@ -780,9 +782,9 @@ struct Collider {
         soa_valid = false;
         const int nw = cur ^ 1;
         // shg.clear() (:262) — only the counters need it; every other array is fully rewritten
-        PS_CUDA_TRY(err, cudaMemsetAsync(cell_count, 0, (uint64_t)ncell * sizeof(uint32_t), st));
+        PS_CUDA_TRY(err, cudaMemsetAsync(cell_count, 0, cell_count_bytes(ncell), st));
         bin_kernel<Real><<<gn, 256, 0, st>>>(rec[cur], n32, k, cell_count, slot_cell, arrival, ds);
-        PS_CUDA_TRY(err, exclusive_scan_u32(cell_count, cell_start, ncell, scan_sums, cell_start + ncell, &ds->max_cell, st));
+        PS_CUDA_TRY(err, exclusive_scan<uint8_t>(reinterpret_cast<const uint8_t*>(cell_count), cell_start, ncell, scan_sums, cell_start + ncell, &ds->max_cell, st));
         place_kernel<<<gn, 256, 0, st>>>(slot_cell, arrival, pid[cur], cell_start, n32, tmp_id);
         move_kernel<Real><<<gn, 256, 0, st>>>(rec[cur], pid[cur], slot_cell, cell_start, tmp_id, n32, k, rec[nw], pid[nw], ds);
         detect_kernel<Real, false><<<gn, 256, 0, st>>>(rec[nw], cell_start, n32, k, entries, entries_cap, head, wl[0], ds, SlabView{});

@@ -54,9 +54,24 @@ __device__ __forceinline__ void load_items(const uint32_t* __restrict__ in, uint
     }
 }
 
+// Same for one-byte items (the per-cell counters are u8 like the reference's grid_array, src/core.zig:51, four to a
+// 32-bit word): 16 items = one 16-byte load.  The buffer is padded to a whole number of 16-byte groups with zeros.
+__device__ __forceinline__ void load_items(const uint8_t* __restrict__ in, uint64_t len, uint64_t start, uint32_t (&x)[SCAN_ITEMS]) {
+    if (start < len) {
+        const uint4 q = *reinterpret_cast<const uint4*>(in + start);
+        const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+        for (int j = 0; j < SCAN_ITEMS; ++j) x[j] = (w[j >> 2] >> ((j & 3) * 8)) & 0xffu;
+    } else {
+#pragma unroll
+        for (int j = 0; j < SCAN_ITEMS; ++j) x[j] = 0u;
+    }
+}
+
 // sums[b] = sum of tile b; optionally track the largest element (max cell population).
+template <class In>
 __global__ void __launch_bounds__(SCAN_THREADS)
-scan_reduce_kernel(const uint32_t* __restrict__ in, uint64_t len, uint32_t* __restrict__ sums, uint32_t* __restrict__ max_out) {
+scan_reduce_kernel(const In* __restrict__ in, uint64_t len, uint32_t* __restrict__ sums, uint32_t* __restrict__ max_out) {
     const uint64_t start = (uint64_t)blockIdx.x * SCAN_TILE + (uint64_t)threadIdx.x * SCAN_ITEMS;
     uint32_t x[SCAN_ITEMS];
     load_items(in, len, start, x);
@@ -101,9 +116,10 @@ scan_spine_kernel(uint32_t* __restrict__ sums, uint32_t nb, uint32_t* __restrict
     if (threadIdx.x == 0) *out_total = carry_sh;
 }
 
-// out[i] = sums[tile] + exclusive prefix within the tile; out may alias in.
+// out[i] = sums[tile] + exclusive prefix within the tile; out may alias in (32-bit items).
+template <class In>
 __global__ void __launch_bounds__(SCAN_THREADS)
-scan_down_kernel(const uint32_t* in, uint64_t len, const uint32_t* __restrict__ sums, uint32_t* out) {
+scan_down_kernel(const In* in, uint64_t len, const uint32_t* __restrict__ sums, uint32_t* out) {
     const uint64_t start = (uint64_t)blockIdx.x * SCAN_TILE + (uint64_t)threadIdx.x * SCAN_ITEMS;
     uint32_t x[SCAN_ITEMS];
     load_items(in, len, start, x);
@@ -128,14 +144,28 @@ scan_down_kernel(const uint32_t* in, uint64_t len, const uint32_t* __restrict__ 
 inline uint64_t scan_tiles(uint64_t len) { return (len + SCAN_TILE - 1) / SCAN_TILE; }
 
 // out[0..len) = exclusive scan of in[0..len); *total_out (device) = sum.  `sums` holds scan_tiles(len) words.
-inline cudaError_t exclusive_scan_u32(const uint32_t* in, uint32_t* out, uint64_t len, uint32_t* sums,
-                                      uint32_t* total_out, uint32_t* max_out, cudaStream_t st) {
+template <class In>
+inline cudaError_t exclusive_scan(const In* in, uint32_t* out, uint64_t len, uint32_t* sums,
+                                  uint32_t* total_out, uint32_t* max_out, cudaStream_t st) {
     if (len == 0) return cudaMemsetAsync(total_out, 0, sizeof(uint32_t), st);
     const uint64_t nb = scan_tiles(len);
-    scan_reduce_kernel<<<(unsigned)nb, SCAN_THREADS, 0, st>>>(in, len, sums, max_out);
+    scan_reduce_kernel<In><<<(unsigned)nb, SCAN_THREADS, 0, st>>>(in, len, sums, max_out);
     scan_spine_kernel<<<1, 1024, 0, st>>>(sums, (uint32_t)nb, total_out);
-    scan_down_kernel<<<(unsigned)nb, SCAN_THREADS, 0, st>>>(in, len, sums, out);
+    scan_down_kernel<In><<<(unsigned)nb, SCAN_THREADS, 0, st>>>(in, len, sums, out);
     return cudaGetLastError();
 }
+inline cudaError_t exclusive_scan_u32(const uint32_t* in, uint32_t* out, uint64_t len, uint32_t* sums,
+                                      uint32_t* total_out, uint32_t* max_out, cudaStream_t st) {
+    return exclusive_scan<uint32_t>(in, out, len, sums, total_out, max_out, st);
+}
+
+// Per-cell counters, one byte each, incremented through the enclosing 32-bit word.  Returns the counter's previous
+// value (the slot the caller gets inside its cell).  A counter that would pass 255 carries into its neighbour: the
+// caller flags that as PS_ERR_CELL_OVERFLOW (the reference's u8 wraps or panics there, src/core.zig:132).
+__device__ __forceinline__ uint32_t cell_count_fetch_inc(uint32_t* __restrict__ count_words, uint32_t c) {
+    const uint32_t sh = (c & 3u) * 8u;
+    return (atomicAdd(count_words + (c >> 2), 1u << sh) >> sh) & 0xffu;
+}
+inline uint64_t cell_count_bytes(uint64_t ncell) { return (ncell + 15) / 16 * 16; }   // whole 16-byte groups
 
 }  // namespace ps

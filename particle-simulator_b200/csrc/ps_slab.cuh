@@ -186,7 +186,7 @@ slab_bin_kernel(const Rec<Real>* __restrict__ rec_old, const uint32_t* __restric
     }
     if (gi >= g.col_off && gi < g.col_off + g.ncl) {                 // stays in the local grid (own or ghost column)
         const uint32_t c = (gi - g.col_off) * g.rows + gj;
-        const uint32_t a = atomicAdd(cell_count + c, 1u);
+        const uint32_t a = cell_count_fetch_inc(cell_count, c);
         slot_cell[t] = c; arrival[t] = a;
         if (a >= 255u) atomicOr(&ds->flags, FLAG_CELL_OVERFLOW);
     } else {
@@ -213,7 +213,7 @@ slab_bin_recv_kernel(void* recv_l, void* recv_r, StepConst<Real> k, SlabGeom g, 
     global_cell<Real>(r.x, r.y, k, g.gcols, gi, gj);
     if (gi >= g.col_off && gi < g.col_off + g.ncl) {
         const uint32_t c = (gi - g.col_off) * g.rows + gj;
-        const uint32_t a = atomicAdd(cell_count + c, 1u);
+        const uint32_t a = cell_count_fetch_inc(cell_count, c);
         slot_cell[g.cap + j] = c; arrival[g.cap + j] = a;
         if (a >= 255u) atomicOr(&ds->flags, FLAG_CELL_OVERFLOW);
     } else {
@@ -456,7 +456,7 @@ struct SlabCollider {
         entries_cap = (uint32_t)ecap;
         int rc;
         for (int i = 0; i < 2; ++i) { if ((rc = alloc(&rec[i], cap))) return rc; if ((rc = alloc(&pid[i], cap))) return rc; }
-        if ((rc = alloc(&cell_count, (uint64_t)ncell_local))) return rc;
+        if ((rc = alloc(&cell_count, cell_count_bytes(ncell_local) / 4))) return rc;
         if ((rc = alloc(&cell_start, (uint64_t)ncell_local + 3))) return rc;
         if ((rc = alloc(&scan_sums, scan_tiles(ncell_local) + 1))) return rc;
         const uint64_t nin = cap + 2ull * g.cap_h;
@@ -612,7 +612,7 @@ struct SlabCollider {
         if (err.status != PS_OK) return err.status;
         k_step = consts();
         cudaStream_t st = stream;
-        PS_CUDA_TRY(err, cudaMemsetAsync(cell_count, 0, (size_t)ncell_local * sizeof(uint32_t), st));
+        PS_CUDA_TRY(err, cudaMemsetAsync(cell_count, 0, cell_count_bytes(ncell_local), st));
         slab_begin_kernel<Real><<<1, 32, 0, st>>>(sd, ds, send_l, send_r);
         own_b_step = last.own_b; n_own_step = last.own_e - last.own_b;   // the layout left by the previous sub-step (host copy)
         slab_bin_kernel<Real><<<(n_own_step + 255) / 256 + 1, 256, 0, st>>>(rec[cur], pid[cur], own_b_step, n_own_step, k_step, g, cell_count, slot_cell, arrival, send_l, send_r, sd, ds);
@@ -630,7 +630,7 @@ struct SlabCollider {
         if (int d = dbg("bin")) return d;
         slab_bin_recv_kernel<Real><<<g_h, 256, 0, st>>>(recv_l, recv_r, k, g, cell_count, slot_cell, arrival, sd, ds);
         if (int d = dbg("bin_recv")) return d;
-        PS_CUDA_TRY(err, exclusive_scan_u32(cell_count, cell_start, ncell_local, scan_sums, cell_start + ncell_local, &ds->max_cell, st));
+        PS_CUDA_TRY(err, exclusive_scan<uint8_t>(reinterpret_cast<const uint8_t*>(cell_count), cell_start, ncell_local, scan_sums, cell_start + ncell_local, &ds->max_cell, st));
         if (int d = dbg("scan")) return d;
         slab_counts_kernel<<<1, 32, 0, st>>>(cell_start, g, sd);
         if (int d = dbg("counts")) return d;
