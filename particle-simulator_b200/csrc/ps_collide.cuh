@@ -557,10 +557,56 @@ __device__ __forceinline__ void resolve_pair(Rec<Real>& I, Rec<Real>& J, const S
 
 constexpr int RESOLVE_THREADS = 256;
 constexpr uint32_t RESOLVE_TAIL = 512;    // work lists this short are finished by one CTA with CTA barriers only
+constexpr uint32_t RESOLVE_SMEM_TAIL = 256; // ... and lists this short stay in shared memory between rounds (deep chains: hundreds of short rounds)
 
-// One round over the work list `wl[0..cnt)`: every item {a, ea} is a particle whose head moved in the
-// previous round (or any particle with a list when r = 0) together with its head entry.  Appends the
-// particles advanced in this round, with their new head entry, to `out`.
+// One work item {a, ea}: a particle whose head moved in the previous round (or any particle with a list when
+// r = 0) together with its head entry.  Runs the pair if it is ready and this thread is the one to run it; returns
+// how many particles advanced (0 or up to 2) with their new work items in `next`.
+// LOCAL = false: several CTAs work on the round, other SMs' writes are read from L2 (ld.global.cg).
+// LOCAL = true: one CTA alone (tail rounds); plain loads may be served by this SM's L1, which the CTA barrier between
+// rounds keeps coherent with the CTA's own writes.  Chains revisit the same few particles round after round, so the
+// L1 hits cut the per-round latency.  (Nothing was loaded through L1 earlier in the kernel, so no stale lines exist.)
+template <class Real, bool LOCAL>
+__device__ __forceinline__ int resolve_item(Rec<Real>* rec, const uint32_t* __restrict__ entries, unsigned long long* head,
+                                            uint2 item, uint32_t r, const StepConst<Real>& k, uint2 (&next)[2]) {
+    const uint32_t a = item.x, ea = item.y;
+    const uint32_t b = ea & ENT_SLOT_MASK;
+    // Round 0: every particle with a visible list is on the work list, and a pair can only be ready if the two
+    // heads name each other, in which case the lower slot's thread runs it.  So the higher slot need not look.
+    if (r == 0u && b < a) return 0;
+    // everything that depends only on the item is requested at once (the records speculatively)
+    const unsigned long long ha = LOCAL ? head[a] : __ldcg(head + a);
+    const unsigned long long hb = LOCAL ? head[b] : __ldcg(head + b);
+    const Rec<Real> Ra = LOCAL ? ld_rec(rec + a) : ld_rec_cg(rec + a), Rb = LOCAL ? ld_rec(rec + b) : ld_rec_cg(rec + b);
+    if (head_stamp(ha) == r + 1) return 0;           // a already ran a pair this round (executed by its partner)
+    if (head_stamp(hb) == r + 1) return 0;           // b moved this round; b is on the next list and will look at a
+    const uint32_t rem_a = head_rem(ha), rem_b = head_rem(hb);
+    if (rem_b == 0) return 0;                        // (rem_a > 0: a is on the list)
+    const uint32_t ia = head_cursor(ha), ib = head_cursor(hb);
+    const uint32_t eb = entries[ib];
+    const uint32_t ea_next = rem_a > 1 ? entries[ia + 1] : 0u;
+    const uint32_t eb_next = rem_b > 1 ? entries[ib + 1] : 0u;
+    // same pair seen from the other side: partner = a, same offset, opposite role
+    if (eb != (a | (ea & (7u << 28)) | (~ea & (1u << 31)))) return 0;
+    // Both particles on this round's list (b's head last moved in round r-1, or never when r = 0): the
+    // lower slot runs the pair.  Membership is read from the SAME 64-bit word as the cursor, so a
+    // concurrent executor cannot make the two threads disagree.
+    if (b < a && head_stamp(hb) == r) return 0;
+    const bool a_centre = (ea >> 31) != 0;           // entry = {particle_i = neighbour, particle_j = centre}
+    Rec<Real> I = a_centre ? Rb : Ra, J = a_centre ? Ra : Rb;
+    resolve_pair<Real>(I, J, k);
+    st_rec(rec + (a_centre ? b : a), I);
+    st_rec(rec + (a_centre ? a : b), J);
+    head[a] = head_word(r + 1, rem_a - 1, ia + 1);
+    head[b] = head_word(r + 1, rem_b - 1, ib + 1);
+    int m = 0;
+    if (rem_a > 1) next[m++] = make_uint2(a, ea_next);
+    if (rem_b > 1) next[m++] = make_uint2(b, eb_next);
+    return m;
+}
+
+// One round over the work list `wl[0..cnt)` by one or many CTAs; appends the particles advanced in this round, with
+// their new head entry, to `out` (buffered per CTA: one global atomic per batch of 256 items).
 template <class Real>
 __device__ __forceinline__ void resolve_round(Rec<Real>* rec, const uint32_t* __restrict__ entries, unsigned long long* head,
                                               const uint2* wl, uint32_t cnt, uint2* out, uint32_t* out_count, uint32_t r,
@@ -570,42 +616,11 @@ __device__ __forceinline__ void resolve_round(Rec<Real>* rec, const uint32_t* __
         if (threadIdx.x == 0) *sh_cnt = 0;
         __syncthreads();
         const uint32_t idx = base + threadIdx.x;
-        do {
-            if (idx >= cnt) break;
-            const uint2 item = __ldcg(wl + idx);
-            const uint32_t a = item.x, ea = item.y;
-            const uint32_t b = ea & ENT_SLOT_MASK;
-            // Round 0: every particle with a visible list is on the work list, and a pair can only be ready if the two
-            // heads name each other, in which case the lower slot's thread runs it.  So the higher slot need not look.
-            if (r == 0u && b < a) break;
-            // everything that depends only on the item is requested at once (the records speculatively)
-            const unsigned long long ha = __ldcg(head + a);
-            const unsigned long long hb = __ldcg(head + b);
-            const Rec<Real> Ra = ld_rec_cg(rec + a), Rb = ld_rec_cg(rec + b);
-            if (head_stamp(ha) == r + 1) break;              // a already ran a pair this round (executed by its partner)
-            if (head_stamp(hb) == r + 1) break;              // b moved this round; b is on the next list and will look at a
-            const uint32_t rem_a = head_rem(ha), rem_b = head_rem(hb);
-            if (rem_b == 0) break;                           // (rem_a > 0: a is on the list)
-            const uint32_t ia = head_cursor(ha), ib = head_cursor(hb);
-            const uint32_t eb = entries[ib];
-            const uint32_t ea_next = rem_a > 1 ? entries[ia + 1] : 0u;
-            const uint32_t eb_next = rem_b > 1 ? entries[ib + 1] : 0u;
-            // same pair seen from the other side: partner = a, same offset, opposite role
-            if (eb != (a | (ea & (7u << 28)) | (~ea & (1u << 31)))) break;
-            // Both particles on this round's list (b's head last moved in round r-1, or never when r = 0): the
-            // lower slot runs the pair.  Membership is read from the SAME 64-bit word as the cursor, so a
-            // concurrent executor cannot make the two threads disagree.
-            if (b < a && head_stamp(hb) == r) break;
-            const bool a_centre = (ea >> 31) != 0;           // entry = {particle_i = neighbour, particle_j = centre}
-            Rec<Real> I = a_centre ? Rb : Ra, J = a_centre ? Ra : Rb;
-            resolve_pair<Real>(I, J, k);
-            st_rec(rec + (a_centre ? b : a), I);
-            st_rec(rec + (a_centre ? a : b), J);
-            head[a] = head_word(r + 1, rem_a - 1, ia + 1);
-            head[b] = head_word(r + 1, rem_b - 1, ib + 1);
-            if (rem_a > 1) sh_buf[atomicAdd(sh_cnt, 1u)] = make_uint2(a, ea_next);
-            if (rem_b > 1) sh_buf[atomicAdd(sh_cnt, 1u)] = make_uint2(b, eb_next);
-        } while (false);
+        if (idx < cnt) {
+            uint2 next[2];
+            const int m = resolve_item<Real, false>(rec, entries, head, __ldcg(wl + idx), r, k, next);
+            for (int i = 0; i < m; ++i) sh_buf[atomicAdd(sh_cnt, 1u)] = next[i];
+        }
         __syncthreads();
         const uint32_t m = *sh_cnt;
         if (m) {                                             // one global atomic per CTA per batch
@@ -645,21 +660,51 @@ resolve_kernel(Rec<Real>* rec, const uint32_t* __restrict__ entries, unsigned lo
         grid.sync();
     }
     if (blockIdx.x != 0) return;
-    // tail phase: CTA 0 alone, CTA barriers only (its own writes reach L2 before the barrier releases)
+    // tail phase: CTA 0 alone, CTA barriers only (its own writes reach L2 before the barrier releases).  A settled
+    // pile has hundreds of short rounds whose cost is a chain of L2 round trips, so while the work list is at most
+    // RESOLVE_SMEM_TAIL items long it lives in shared memory: no list loads, no counters, no atomics in global memory.
+    __shared__ uint2 sh_items[2][2 * RESOLVE_SMEM_TAIL];
+    __shared__ uint32_t sh_n[2];
+    bool in_smem = false;
+    uint32_t cnt_smem = 0;
     for (;; ++r) {
-        const uint32_t cur = r % 3, nxt = (r + 1) % 3, nn = (r + 2) % 3;
-        const uint32_t cnt = __ldcg(&ds->wl_count[cur]);
+        const uint32_t cur = r % 3, nxt = (r + 1) % 3, nn = (r + 2) % 3, sc = r & 1u, sn = sc ^ 1u;
+        uint32_t cnt = in_smem ? cnt_smem : __ldcg(&ds->wl_count[cur]);
         if (trace && r < 64) { ds->trace_cnt[r] = cnt; ds->trace_ns[r] = (uint32_t)(global_ns() - t_begin); }
         if (cnt == 0 || r + 2 >= HEAD_STAMP_MAX) break;
-        __syncthreads();                                     // everyone has read cnt before the counters move on
-        if (threadIdx.x == 0) ds->wl_count[nn] = 0;
-        resolve_round<Real>(rec, entries, head, lists[cur], cnt, lists[nxt], &ds->wl_count[nxt], r,
-                            0u, RESOLVE_THREADS, k, sh_buf, &sh_cnt, &sh_base);
-        __threadfence();
-        __syncthreads();
+        __syncthreads();                                     // everyone has read the count before anything moves on
+        if (!in_smem && cnt <= RESOLVE_SMEM_TAIL) {          // short enough: pull the list into shared memory
+            for (uint32_t i = threadIdx.x; i < cnt; i += RESOLVE_THREADS) sh_items[sc][i] = __ldcg(lists[cur] + i);
+            in_smem = true;
+            __syncthreads();
+        } else if (in_smem && cnt > RESOLVE_SMEM_TAIL) {     // grew again (rare): push it back to the global list
+            for (uint32_t i = threadIdx.x; i < cnt; i += RESOLVE_THREADS) lists[cur][i] = sh_items[sc][i];
+            if (threadIdx.x == 0) { ds->wl_count[cur] = cnt; ds->wl_count[nxt] = 0; }
+            in_smem = false;
+            __threadfence();
+            __syncthreads();
+        }
+        if (in_smem) {
+            if (threadIdx.x == 0) sh_n[sn] = 0;
+            __syncthreads();
+            if (threadIdx.x < cnt) {                         // cnt <= RESOLVE_SMEM_TAIL <= RESOLVE_THREADS: one item per thread
+                uint2 next[2];
+                const int m = resolve_item<Real, true>(rec, entries, head, sh_items[sc][threadIdx.x], r, k, next);
+                for (int i = 0; i < m; ++i) sh_items[sn][atomicAdd(&sh_n[sn], 1u)] = next[i];
+            }
+            __syncthreads();                                 // makes this round's global writes visible to the whole CTA
+            cnt_smem = sh_n[sn];                             // at most 2 * cnt items: fits the buffer
+        } else {
+            if (threadIdx.x == 0) ds->wl_count[nn] = 0;
+            resolve_round<Real>(rec, entries, head, lists[cur], cnt, lists[nxt], &ds->wl_count[nxt], r,
+                                0u, RESOLVE_THREADS, k, sh_buf, &sh_cnt, &sh_base);
+            __threadfence();
+            __syncthreads();
+        }
     }
+    const bool stamps_exhausted = (in_smem ? cnt_smem : __ldcg(&ds->wl_count[r % 3])) != 0;
     if (threadIdx.x == 0) {
-        if (ds->wl_count[r % 3] != 0) atomicOr(&ds->flags, FLAG_CAPACITY);   // ran out of round stamps (never in practice)
+        if (stamps_exhausted) atomicOr(&ds->flags, FLAG_CAPACITY);          // ran out of round stamps (never in practice)
         ds->rounds_last = r;
         if (trace) ds->trace_rounds = r < 63 ? r + 1 : 64;
         ds->rounds_total += r - r_start;
