@@ -24,13 +24,15 @@
 //            exactly in the order the reference's pair list (:164-209) mentions that particle.  The
 //            position of an entry in the global list is the lexicographic key (centre slot, offset
 //            index, neighbour slot), so each particle's own sub-list is produced without
-//            materialising or sorting the global list.  One kernel: count, block scan, one atomic
-//            per CTA for the base, second walk (L1-resident) writes the entries.
+//            materialising or sorting the global list.  One kernel: every candidate tested once, the
+//            hits kept as a bit mask; CTA scan + one atomic per CTA reserves list space; the mask is
+//            replayed in list order.
 //   resolve  a pair may run as soon as it heads BOTH of its particles' sub-lists: pairs that share
 //            no particle commute, so executing all such "ready" pairs together, round after round,
 //            is bit-identical to the sequential loop.  One persistent cooperative kernel runs the
 //            rounds (one grid barrier each) over work lists that hold only the particles whose head
-//            changed in the previous round, so total work is O(pairs).
+//            changed in the previous round, so total work is O(pairs).  Short lists are finished by
+//            one CTA, the shortest out of shared memory and L1 (deep chains = many short rounds).
 #pragma once
 #include <cooperative_groups.h>
 
