@@ -414,6 +414,28 @@ def run_extras(torch, sim, scene, hp, hv, n, S, prec):
                                        "note": "BASELINE.json configs[3]: full updatePhysics with exact-order resolve"}
     except Exception as e:
         out["collide_16Mi_f32"] = {"error": str(e)}
+    # the faithful updatePhysics (collisions on, f64) on the CPU port, and the same scenes on the GPU
+    try:
+        import oracle
+
+        for name, cs, substeps in (("default_13k", scenes.default_scene(), 1000), ("1Mi", scenes.scaled_scene(1 << 20), 24)):
+            pos, vel = scenes.spawn(cs, seed=1)
+            params = oracle.make_params(radius=cs.radius, width=cs.width, height=cs.height, grid_size=cs.grid_size)
+            p, v = pos.copy(), vel.copy()
+            secs = oracle.run(params, p, v, substeps, collisions=True)["seconds"]
+            with Simulation(cs, precision="f64", collisions=True) as c:
+                c.set_stream(stream)
+                c.upload(pos, vel)
+                c.step_substeps(8)
+                c.upload(pos, vel)
+                ms = timed(torch, None, lambda: c.step_substeps(substeps), 1)
+                gp, gv = c.download()
+            out[f"collide_{name}_f64"] = {"cpu_port_updates_per_s": cs.count * substeps / secs, "gpu_updates_per_s": cs.count * substeps / (ms * 1e-3),
+                                          "substeps": substeps, "bit_identical": bool(np.array_equal(gp.view(np.uint8), p.view(np.uint8)) and
+                                                                                      np.array_equal(gv.view(np.uint8), v.view(np.uint8))),
+                                          "note": "full updatePhysics with collisions, f64: oracle/core_ref.hpp single thread vs libparticles_cuda (device-resident)"}
+    except Exception as e:
+        out["collide_cpu_compare"] = {"error": str(e)}
     return out
 
 
