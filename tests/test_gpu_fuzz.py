@@ -1,0 +1,82 @@
+"""Randomised differential tests: many small scenes with random shapes, densities, cell sizes, gravity toggles and
+precisions, each run through libparticles_cuda (single handle, and slab-decomposed with a random number of emulated
+ranks) and through the oracle; positions and velocities must agree bit for bit.  Seeds are fixed: the cases are the
+same on every run."""
+import numpy as np
+import pytest
+
+from _util import DTYPES, assert_bit_exact, run_oracle
+from particle_simulator_b200 import Simulation, SlabGroup, scenes
+
+pytestmark = pytest.mark.gpu
+
+
+def random_case(seed):
+    rng = np.random.default_rng(1000 + seed)
+    radius = float(rng.choice([1.0, 1.5, 2.0, 2.5, 3.0]))
+    grid = float(rng.choice([2.0 * radius, 2.0 * radius, 2.0 * radius + 0.5, 2.5 * radius]))   # >= 2r, sometimes not the reference's 2r
+    cols, rows = int(rng.integers(6, 70)), int(rng.integers(4, 60))
+    width = cols * grid + float(rng.uniform(0, grid * 0.9))          # worlds that are not multiples of the cell
+    height = rows * grid + float(rng.uniform(0, grid * 0.9))
+    density = float(rng.choice([0.2, 0.45, 0.45, 1.0, 2.0]))
+    n = max(1, int(cols * rows * density))
+    scene = scenes.Scene(count=n, radius=radius, width=width, height=height, grid_size=grid,
+                         g=float(rng.choice([50.0, 0.0, 200.0, 1e-7])),   # 1e-7 exercises zeroNearZero (src/core.zig:242-244)
+                         boundary_damping=float(rng.choice([0.1, 0.5, 1.0])), particle_damping=float(rng.choice([0.9, 0.5, 0.0])),
+                         sub_steps=int(rng.choice([8, 4, 3])), target_fps=float(rng.choice([60.0, 30.0, 144.0])),
+                         vel_min=-float(rng.choice([640.0, 100.0])), vel_max=float(rng.choice([640.0, 100.0])))
+    precision = "f64" if rng.random() < 0.5 else "f32"
+    plan = [(int(rng.integers(1, 4)), bool(rng.random() < 0.5)) for _ in range(int(rng.integers(1, 5)))]   # (frames, gravity)
+    return scene, precision, plan, int(rng.integers(1, 1 << 30)), int(rng.integers(1, 6))
+
+
+@pytest.mark.parametrize("seed", range(40))
+def test_random_scene_single_handle(seed):
+    scene, precision, plan, spawn_seed, _ = random_case(seed)
+    dt = DTYPES[precision]
+    pos0, vel0 = scenes.spawn(scene, seed=spawn_seed, dtype=dt)
+    p, v = pos0, vel0
+    for frames, t_acc in plan:
+        p, v, out = run_oracle(scene, p, v, frames * scene.sub_steps, collisions=True, t_acc=t_acc)
+        if out["stats"]["cell_overflow"]:
+            pytest.skip("scene exceeds the reference's u8 cell counter")
+    with Simulation(scene, precision=precision, collisions=True, contacts_per_particle=96) as sim:
+        sim.upload(pos0, vel0)
+        for frames, t_acc in plan:
+            sim.set_acc(t_acc)
+            sim.step(frames)
+        got_p, got_v = sim.download(dtype=dt)
+    assert_bit_exact(got_p, p, f"positions (seed {seed})")
+    assert_bit_exact(got_v, v, f"velocities (seed {seed})")
+
+
+@pytest.mark.parametrize("seed", range(40, 64))
+def test_random_scene_emulated_slabs(seed):
+    scene, precision, plan, spawn_seed, nranks = random_case(seed)
+    cols = int(scene.width) // int(scene.grid_size)
+    nranks = max(1, min(nranks, cols // 3))                       # every rank needs a few cell columns
+    dt = DTYPES[precision]
+    pos0, vel0 = scenes.spawn(scene, seed=spawn_seed)
+    p, v = pos0.astype(dt), vel0.astype(dt)
+    for frames, t_acc in plan:
+        p, v, out = run_oracle(scene, p, v, frames * scene.sub_steps, collisions=True, t_acc=t_acc)
+        if out["stats"]["cell_overflow"]:
+            pytest.skip("scene exceeds the reference's u8 cell counter")
+    try:
+        with SlabGroup(scene, nranks, precision=precision, contacts_per_particle=96) as g:
+            g.upload_global(pos0, vel0)
+            for frames, t_acc in plan:
+                g.set_acc(t_acc)
+                g.step_substeps(frames * scene.sub_steps)
+            parts = [g.download_owned(r) for r in range(nranks)]
+    except Exception as e:
+        if "crossed a whole" in str(e) or "halo" in str(e):
+            pytest.skip(f"scene too violent for {nranks} narrow slabs: {e}")
+        raise
+    got_p = np.full((scene.count, 2), np.nan); got_v = np.full((scene.count, 2), np.nan)
+    seen = np.zeros(scene.count, dtype=int)
+    for ids, pp, vv in parts:
+        got_p[ids.astype(np.int64)] = pp; got_v[ids.astype(np.int64)] = vv; seen[ids.astype(np.int64)] += 1
+    assert (seen == 1).all()
+    assert_bit_exact(got_p.astype(dt), p, f"positions (seed {seed}, {nranks} ranks)")
+    assert_bit_exact(got_v.astype(dt), v, f"velocities (seed {seed}, {nranks} ranks)")
