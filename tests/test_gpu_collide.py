@@ -178,3 +178,11 @@ def test_grid_size_not_a_power_of_two(precision, radius, grid_size):
     (src/core.zig:61-67 vs :104-105), so the last column and row absorb the clamp."""
     scene = scenes.Scene(count=3000, radius=radius, width=400.0, height=300.0, grid_size=grid_size)
     check(scene, 9, 80, precision, False, contacts_per_particle=48)
+
+
+@pytest.mark.parametrize("precision", ["f64", "f32"])
+def test_cell_smaller_than_the_interaction_range(precision):
+    """grid_size < 2r: the reference still looks at the half stencil of adjacent cells only (src/core.zig:58,180-205) and
+    therefore misses overlapping pairs that sit two cells apart.  The library must miss exactly the same pairs."""
+    scene = scenes.Scene(count=2500, radius=2.0, width=300.0, height=240.0, grid_size=3.0)
+    check(scene, 11, 60, precision, True, contacts_per_particle=64)
