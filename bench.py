@@ -54,6 +54,17 @@ def parse_args():
     return ap.parse_args()
 
 
+def host_cpu_model():
+    try:
+        with open("/proc/cpuinfo") as f:
+            for line in f:
+                if line.lower().startswith("model name"):
+                    return line.split(":", 1)[1].strip()
+    except OSError:
+        pass
+    return "unknown"
+
+
 def env_int(name, default):
     try:
         return int(os.environ.get(name, default))
@@ -122,7 +133,7 @@ def run_reference(args):
         "data": "synthetic",
         "config": workload_config(args, "f64"),
         "cpu_baseline": {"value": rate, "unit": UNIT, "cores": 1, "kind": "port", "sample": sample,
-                         "host_cpus": os.cpu_count()},
+                         "host_cpus": os.cpu_count(), "host_cpu_model": host_cpu_model()},
         "e2e": {"value": rate, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "note": "Zig toolchain absent: the reference arm is oracle/core_ref.hpp, a C++ restatement of src/core.zig "
                 "(g++ -O2 -ffp-contract=off); parity with the Zig binary is unpinned",
@@ -340,7 +351,7 @@ def run_ours(args):
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         n_s = min(n, 16 << 20)
         rate, total, _ = cpu_reference_rate(scene_all, n_s, frames=4, warm_frames=0, dtype=np.float64)
-        cpu = {"value": rate, "unit": UNIT, "cores": 1, "kind": "port", "host_cpus": os.cpu_count(),
+        cpu = {"value": rate, "unit": UNIT, "cores": 1, "kind": "port", "host_cpus": os.cpu_count(), "host_cpu_model": host_cpu_model(),
                "sample": f"{n_s} of the {n} particles, 4 updatePhysics frames (32 sub-steps) of integrate + wall bounce in f64 "
                          f"(core.zig as written), oracle/core_ref.hpp single thread, {total:.1f} s of CPU work"}
 
