@@ -159,30 +159,58 @@ rec_to_soa_kernel(const uint32_t* __restrict__ pid, const Rec<Real>* __restrict_
 }
 
 // ---- bin: integrate + bounce + cell key + per-cell count ------------------------------------
+constexpr int SORT_ILP = 2;
 template <class Real>
 __global__ void __launch_bounds__(256)
 bin_kernel(const Rec<Real>* __restrict__ rec_old, uint32_t n, StepConst<Real> k, uint32_t* __restrict__ cell_count,
            uint32_t* __restrict__ slot_cell, uint32_t* __restrict__ arrival, DevState* __restrict__ ds) {
-    const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
-    if (s == 0) ds->entries_used = 0;                           // detect of this sub-step allocates from zero
-    if (s >= n) return;
-    Rec<Real> r = ld_rec(rec_old + s);
-    integrate_rec<Real>(r, k);
-    const uint32_t c = cell_of<Real>(r.x, r.y, k);
-    const uint32_t a = cell_count_fetch_inc(cell_count, c);     // grid_array[c] += 1   src/core.zig:132 (u8 counters, :51)
-    slot_cell[s] = c;
-    arrival[s] = a;
-    if (a >= 255u) atomicOr(&ds->flags, FLAG_CELL_OVERFLOW);    // the reference's u8 would wrap here
+    // SORT_ILP slots per thread, CTA-strided: the loads, then the counting atomics, of all of them are in flight together
+    const uint32_t s0 = blockIdx.x * (blockDim.x * SORT_ILP) + threadIdx.x;
+    if (s0 == 0) ds->entries_used = 0;                          // detect of this sub-step allocates from zero
+    Rec<Real> r[SORT_ILP];
+    uint32_t c[SORT_ILP], a[SORT_ILP];
+#pragma unroll
+    for (int j = 0; j < SORT_ILP; ++j) { const uint32_t s = s0 + j * blockDim.x; if (s < n) r[j] = ld_rec(rec_old + s); }
+#pragma unroll
+    for (int j = 0; j < SORT_ILP; ++j) {
+        const uint32_t s = s0 + j * blockDim.x;
+        if (s < n) {
+            integrate_rec<Real>(r[j], k);
+            c[j] = cell_of<Real>(r[j].x, r[j].y, k);
+            a[j] = cell_count_fetch_inc(cell_count, c[j]);      // grid_array[c] += 1   src/core.zig:132 (u8 counters, :51)
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < SORT_ILP; ++j) {
+        const uint32_t s = s0 + j * blockDim.x;
+        if (s < n) {
+            slot_cell[s] = c[j];
+            arrival[s] = a[j];
+            if (a[j] >= 255u) atomicOr(&ds->flags, FLAG_CELL_OVERFLOW);   // the reference's u8 would wrap here
+        }
+    }
 }
 
 // ---- place + move: the stable counting sort ----------------------------------------------------
 __global__ void __launch_bounds__(256)
 place_kernel(const uint32_t* __restrict__ slot_cell, const uint32_t* __restrict__ arrival, const uint32_t* __restrict__ pid_old,
              const uint32_t* __restrict__ cell_start, uint32_t n, uint32_t* __restrict__ tmp_id) {
-    const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
-    if (s >= n) return;
-    const uint32_t dst = cell_start[slot_cell[s]] + arrival[s];
-    if (dst < n) tmp_id[dst] = pid_old[s];                      // out of range only after a flagged counter overflow
+    const uint32_t s0 = blockIdx.x * (blockDim.x * SORT_ILP) + threadIdx.x;
+    uint32_t c[SORT_ILP], a[SORT_ILP], id[SORT_ILP], b[SORT_ILP];
+#pragma unroll
+    for (int j = 0; j < SORT_ILP; ++j) {
+        const uint32_t s = s0 + j * blockDim.x;
+        if (s < n) { c[j] = slot_cell[s]; a[j] = arrival[s]; id[j] = pid_old[s]; }
+    }
+#pragma unroll
+    for (int j = 0; j < SORT_ILP; ++j) if (s0 + j * blockDim.x < n) b[j] = cell_start[c[j]];
+#pragma unroll
+    for (int j = 0; j < SORT_ILP; ++j) {
+        if (s0 + j * blockDim.x < n) {
+            const uint32_t dst = b[j] + a[j];
+            if (dst < n) tmp_id[dst] = id[j];                   // out of range only after a flagged counter overflow
+        }
+    }
 }
 
 template <class Real>
@@ -190,23 +218,34 @@ __global__ void __launch_bounds__(256)
 move_kernel(const Rec<Real>* __restrict__ rec_old, const uint32_t* __restrict__ pid_old, const uint32_t* __restrict__ slot_cell,
             const uint32_t* __restrict__ cell_start, const uint32_t* __restrict__ tmp_id, uint32_t n, StepConst<Real> k,
             Rec<Real>* __restrict__ rec_new, uint32_t* __restrict__ pid_new, const DevState* __restrict__ ds) {
-    const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
-    if (s >= n) return;
+    const uint32_t s0 = blockIdx.x * (blockDim.x * SORT_ILP) + threadIdx.x;
     if (ds->flags) {                                         // an earlier sub-step failed: the state stays frozen where it failed
-        st_rec(rec_new + s, ld_rec(rec_old + s));
-        pid_new[s] = pid_old[s];
+#pragma unroll
+        for (int j = 0; j < SORT_ILP; ++j) {
+            const uint32_t s = s0 + j * blockDim.x;
+            if (s < n) { st_rec(rec_new + s, ld_rec(rec_old + s)); pid_new[s] = pid_old[s]; }
+        }
         return;
     }
-    const uint32_t id = pid_old[s];
-    const uint32_t c = slot_cell[s];
-    const uint32_t b = cell_start[c], e = cell_start[c + 1];
-    uint32_t rank = 0;
-    for (uint32_t t = b; t < e && t < n; ++t) rank += tmp_id[t] < id ? 1u : 0u;   // ascending index inside the cell, src/core.zig:146-158
-    Rec<Real> r = ld_rec(rec_old + s);
-    integrate_rec<Real>(r, k);                                            // same arithmetic as bin_kernel, bit for bit
-    if (b + rank >= n) return;                                            // only after a flagged counter overflow
-    st_rec(rec_new + b + rank, r);
-    pid_new[b + rank] = id;
+    uint32_t id[SORT_ILP], c[SORT_ILP], b[SORT_ILP], e[SORT_ILP];
+    Rec<Real> r[SORT_ILP];
+#pragma unroll
+    for (int j = 0; j < SORT_ILP; ++j) {
+        const uint32_t s = s0 + j * blockDim.x;
+        if (s < n) { id[j] = pid_old[s]; c[j] = slot_cell[s]; r[j] = ld_rec(rec_old + s); }
+    }
+#pragma unroll
+    for (int j = 0; j < SORT_ILP; ++j) if (s0 + j * blockDim.x < n) { b[j] = cell_start[c[j]]; e[j] = cell_start[c[j] + 1]; }
+#pragma unroll
+    for (int j = 0; j < SORT_ILP; ++j) {
+        if (s0 + j * blockDim.x >= n) continue;
+        uint32_t rank = 0;
+        for (uint32_t t = b[j]; t < e[j] && t < n; ++t) rank += tmp_id[t] < id[j] ? 1u : 0u;   // ascending index inside the cell, src/core.zig:146-158
+        integrate_rec<Real>(r[j], k);                                     // same arithmetic as bin_kernel, bit for bit
+        if (b[j] + rank >= n) continue;                                   // only after a flagged counter overflow
+        st_rec(rec_new + b[j] + rank, r[j]);
+        pid_new[b[j] + rank] = id[j];
+    }
 }
 
 // ---- detect ----------------------------------------------------------------------------------
@@ -830,10 +869,10 @@ struct Collider {
         const int nw = cur ^ 1;
         // shg.clear() (:262) — only the counters need it; every other array is fully rewritten
         PS_CUDA_TRY(err, cudaMemsetAsync(cell_count, 0, cell_count_bytes(ncell), st));
-        bin_kernel<Real><<<gn, 256, 0, st>>>(rec[cur], n32, k, cell_count, slot_cell, arrival, ds);
+        bin_kernel<Real><<<(gn + SORT_ILP - 1) / SORT_ILP, 256, 0, st>>>(rec[cur], n32, k, cell_count, slot_cell, arrival, ds);
         PS_CUDA_TRY(err, exclusive_scan<uint8_t>(reinterpret_cast<const uint8_t*>(cell_count), cell_start, ncell, scan_sums, cell_start + ncell, &ds->max_cell, st));
-        place_kernel<<<gn, 256, 0, st>>>(slot_cell, arrival, pid[cur], cell_start, n32, tmp_id);
-        move_kernel<Real><<<gn, 256, 0, st>>>(rec[cur], pid[cur], slot_cell, cell_start, tmp_id, n32, k, rec[nw], pid[nw], ds);
+        place_kernel<<<(gn + SORT_ILP - 1) / SORT_ILP, 256, 0, st>>>(slot_cell, arrival, pid[cur], cell_start, n32, tmp_id);
+        move_kernel<Real><<<(gn + SORT_ILP - 1) / SORT_ILP, 256, 0, st>>>(rec[cur], pid[cur], slot_cell, cell_start, tmp_id, n32, k, rec[nw], pid[nw], ds);
         detect_kernel<Real, false><<<gn, 256, 0, st>>>(rec[nw], cell_start, n32, k, entries, entries_cap, head, wl[0], ds, SlabView{});
         *launches += 7;
         if (capture) {
