@@ -30,7 +30,7 @@ def random_case(seed):
     return scene, precision, plan, int(rng.integers(1, 1 << 30)), int(rng.integers(1, 6))
 
 
-@pytest.mark.parametrize("seed", range(40))
+@pytest.mark.parametrize("seed", range(100))
 def test_random_scene_single_handle(seed):
     scene, precision, plan, spawn_seed, _ = random_case(seed)
     dt = DTYPES[precision]
@@ -50,7 +50,7 @@ def test_random_scene_single_handle(seed):
     assert_bit_exact(got_v, v, f"velocities (seed {seed})")
 
 
-@pytest.mark.parametrize("seed", range(40, 64))
+@pytest.mark.parametrize("seed", range(100, 160))
 def test_random_scene_emulated_slabs(seed):
     scene, precision, plan, spawn_seed, nranks = random_case(seed)
     cols = int(scene.width) // int(scene.grid_size)
