@@ -596,7 +596,8 @@ __device__ __forceinline__ void resolve_pair(Rec<Real>& I, Rec<Real>& J, const S
     J.u = J.u + nx * kk; J.w = J.w + ny * kk;                                 // :391
 }
 
-constexpr int RESOLVE_THREADS = 256;
+constexpr int RESOLVE_THREADS = 1024;     // one CTA per SM in the grid phase: the grid barrier has 148 participants
+constexpr int RESOLVE_TAIL_THREADS = 256; // the single-CTA tail keeps 8 warps (a CTA barrier among 32 warps is slower)
 constexpr uint32_t RESOLVE_TAIL = 512;    // work lists this short are finished by one CTA with CTA barriers only
 constexpr uint32_t RESOLVE_SMEM_TAIL = 256; // ... and lists this short stay in shared memory between rounds (deep chains: hundreds of short rounds)
 
@@ -651,7 +652,7 @@ __device__ __forceinline__ int resolve_item(Rec<Real>* rec, const uint32_t* __re
 template <class Real>
 __device__ __forceinline__ void resolve_round(Rec<Real>* rec, const uint32_t* __restrict__ entries, unsigned long long* head,
                                               const uint2* wl, uint32_t cnt, uint2* out, uint32_t* out_count, uint32_t r,
-                                              uint32_t first, uint32_t stride, const StepConst<Real>& k,
+                                              uint32_t first, uint32_t stride, uint32_t cta_threads, const StepConst<Real>& k,
                                               uint2* sh_buf, uint32_t* sh_cnt, uint32_t* sh_base) {
     for (uint32_t base = first; base < cnt; base += stride) {
         if (threadIdx.x == 0) *sh_cnt = 0;
@@ -667,7 +668,7 @@ __device__ __forceinline__ void resolve_round(Rec<Real>* rec, const uint32_t* __
         if (m) {                                             // one global atomic per CTA per batch
             if (threadIdx.x == 0) *sh_base = atomicAdd(out_count, m);
             __syncthreads();
-            for (uint32_t i = threadIdx.x; i < m; i += RESOLVE_THREADS) out[*sh_base + i] = sh_buf[i];
+            for (uint32_t i = threadIdx.x; i < m; i += cta_threads) out[*sh_base + i] = sh_buf[i];
         }
         __syncthreads();
     }
@@ -697,10 +698,10 @@ resolve_kernel(Rec<Real>* rec, const uint32_t* __restrict__ entries, unsigned lo
         if (cnt <= RESOLVE_TAIL) break;                      // same value in every thread: the whole grid leaves together
         if (leader) ds->wl_count[nn] = 0;                    // consumed in round r-1, refilled in round r+1
         resolve_round<Real>(rec, entries, head, lists[cur], cnt, lists[nxt], &ds->wl_count[nxt], r,
-                            blockIdx.x * RESOLVE_THREADS, gridDim.x * RESOLVE_THREADS, k, sh_buf, &sh_cnt, &sh_base);
+                            blockIdx.x * RESOLVE_THREADS, gridDim.x * RESOLVE_THREADS, RESOLVE_THREADS, k, sh_buf, &sh_cnt, &sh_base);
         grid.sync();
     }
-    if (blockIdx.x != 0) return;
+    if (blockIdx.x != 0 || threadIdx.x >= RESOLVE_TAIL_THREADS) return;     // exited threads count as arrived at later CTA barriers
     // tail phase: CTA 0 alone, CTA barriers only (its own writes reach L2 before the barrier releases).  A settled
     // pile has hundreds of short rounds whose cost is a chain of L2 round trips, so while the work list is at most
     // RESOLVE_SMEM_TAIL items long it lives in shared memory: no list loads, no counters, no atomics in global memory.
@@ -715,11 +716,11 @@ resolve_kernel(Rec<Real>* rec, const uint32_t* __restrict__ entries, unsigned lo
         if (cnt == 0 || r + 2 >= HEAD_STAMP_MAX) break;
         __syncthreads();                                     // everyone has read the count before anything moves on
         if (!in_smem && cnt <= RESOLVE_SMEM_TAIL) {          // short enough: pull the list into shared memory
-            for (uint32_t i = threadIdx.x; i < cnt; i += RESOLVE_THREADS) sh_items[sc][i] = __ldcg(lists[cur] + i);
+            for (uint32_t i = threadIdx.x; i < cnt; i += RESOLVE_TAIL_THREADS) sh_items[sc][i] = __ldcg(lists[cur] + i);
             in_smem = true;
             __syncthreads();
         } else if (in_smem && cnt > RESOLVE_SMEM_TAIL) {     // grew again (rare): push it back to the global list
-            for (uint32_t i = threadIdx.x; i < cnt; i += RESOLVE_THREADS) lists[cur][i] = sh_items[sc][i];
+            for (uint32_t i = threadIdx.x; i < cnt; i += RESOLVE_TAIL_THREADS) lists[cur][i] = sh_items[sc][i];
             if (threadIdx.x == 0) { ds->wl_count[cur] = cnt; ds->wl_count[nxt] = 0; }
             in_smem = false;
             __threadfence();
@@ -728,7 +729,7 @@ resolve_kernel(Rec<Real>* rec, const uint32_t* __restrict__ entries, unsigned lo
         if (in_smem) {
             if (threadIdx.x == 0) sh_n[sn] = 0;
             __syncthreads();
-            if (threadIdx.x < cnt) {                         // cnt <= RESOLVE_SMEM_TAIL <= RESOLVE_THREADS: one item per thread
+            if (threadIdx.x < cnt) {                         // cnt <= RESOLVE_SMEM_TAIL <= RESOLVE_TAIL_THREADS: one item per thread
                 uint2 next[2];
                 const int m = resolve_item<Real, true>(rec, entries, head, sh_items[sc][threadIdx.x], r, k, next);
                 for (int i = 0; i < m; ++i) sh_items[sn][atomicAdd(&sh_n[sn], 1u)] = next[i];
@@ -738,7 +739,7 @@ resolve_kernel(Rec<Real>* rec, const uint32_t* __restrict__ entries, unsigned lo
         } else {
             if (threadIdx.x == 0) ds->wl_count[nn] = 0;
             resolve_round<Real>(rec, entries, head, lists[cur], cnt, lists[nxt], &ds->wl_count[nxt], r,
-                                0u, RESOLVE_THREADS, k, sh_buf, &sh_cnt, &sh_base);
+                                0u, RESOLVE_TAIL_THREADS, RESOLVE_TAIL_THREADS, k, sh_buf, &sh_cnt, &sh_base);
             __threadfence();
             __syncthreads();
         }
