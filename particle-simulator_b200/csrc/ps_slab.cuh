@@ -166,31 +166,47 @@ slab_bin_kernel(const Rec<Real>* __restrict__ rec_old, const uint32_t* __restric
                 StepConst<Real> k, SlabGeom g,
                 uint32_t* __restrict__ cell_count, uint32_t* __restrict__ slot_cell, uint32_t* __restrict__ arrival,
                 void* send_l, void* send_r, SlabDev* __restrict__ sd, DevState* __restrict__ ds) {
-    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= n_own_prev) return;                                     // the owned range is known on the host: no dependent load
-    const uint32_t s = own_b_prev + t;
-    Rec<Real> r = ld_rec(rec_old + s);
-    if (!ds->flags) integrate_rec<Real>(r, k);                      // error state: the state stays frozen
-    uint32_t gi, gj;
-    global_cell<Real>(r.x, r.y, k, g.gcols, gi, gj);
-    if (gi < g.xlo || gi >= g.xhi) atomicOr(&sd->err, SLAB_ERR_MIGRATION);
-    if (g.gl && gi <= g.x0) {                                        // migrant (gi < x0) or halo (gi == x0) for the left rank
-        const uint32_t j = atomicAdd(&reinterpret_cast<HaloHeader*>(send_l)->count, 1u);
-        if (j < g.cap_h) { st_rec(halo_recs<Real>(send_l) + j, r); halo_pids<Real>(send_l, g.cap_h)[j] = pid_old[s]; }
-        else atomicOr(&sd->err, SLAB_ERR_HALO);
+    // SORT_ILP inputs per thread, CTA-strided: their loads, then their counting atomics, are in flight together.
+    // The owned range is known on the host, so no thread waits for a count from memory first.
+    const uint32_t t0 = blockIdx.x * (blockDim.x * SORT_ILP) + threadIdx.x;
+    Rec<Real> r[SORT_ILP];
+    uint32_t c[SORT_ILP], a[SORT_ILP];
+#pragma unroll
+    for (int j = 0; j < SORT_ILP; ++j) { const uint32_t t = t0 + j * blockDim.x; if (t < n_own_prev) r[j] = ld_rec(rec_old + own_b_prev + t); }
+    const bool frozen = ds->flags != 0u;                             // error state: the state stays frozen
+#pragma unroll
+    for (int j = 0; j < SORT_ILP; ++j) {
+        const uint32_t t = t0 + j * blockDim.x;
+        c[j] = SLAB_INVALID;
+        if (t >= n_own_prev) continue;
+        const uint32_t s = own_b_prev + t;
+        if (!frozen) integrate_rec<Real>(r[j], k);
+        uint32_t gi, gj;
+        global_cell<Real>(r[j].x, r[j].y, k, g.gcols, gi, gj);
+        if (gi < g.xlo || gi >= g.xhi) atomicOr(&sd->err, SLAB_ERR_MIGRATION);
+        if (g.gl && gi <= g.x0) {                                    // migrant (gi < x0) or halo (gi == x0) for the left rank
+            const uint32_t q = atomicAdd(&reinterpret_cast<HaloHeader*>(send_l)->count, 1u);
+            if (q < g.cap_h) { st_rec(halo_recs<Real>(send_l) + q, r[j]); halo_pids<Real>(send_l, g.cap_h)[q] = pid_old[s]; }
+            else atomicOr(&sd->err, SLAB_ERR_HALO);
+        }
+        if (g.gr && gi + 1 >= g.x1) {                                // migrant (gi >= x1) or halo (gi == x1-1) for the right rank
+            const uint32_t q = atomicAdd(&reinterpret_cast<HaloHeader*>(send_r)->count, 1u);
+            if (q < g.cap_h) { st_rec(halo_recs<Real>(send_r) + q, r[j]); halo_pids<Real>(send_r, g.cap_h)[q] = pid_old[s]; }
+            else atomicOr(&sd->err, SLAB_ERR_HALO);
+        }
+        if (gi >= g.col_off && gi < g.col_off + g.ncl) c[j] = (gi - g.col_off) * g.rows + gj;   // stays in the local grid (own or ghost column)
     }
-    if (g.gr && gi + 1 >= g.x1) {                                    // migrant (gi >= x1) or halo (gi == x1-1) for the right rank
-        const uint32_t j = atomicAdd(&reinterpret_cast<HaloHeader*>(send_r)->count, 1u);
-        if (j < g.cap_h) { st_rec(halo_recs<Real>(send_r) + j, r); halo_pids<Real>(send_r, g.cap_h)[j] = pid_old[s]; }
-        else atomicOr(&sd->err, SLAB_ERR_HALO);
-    }
-    if (gi >= g.col_off && gi < g.col_off + g.ncl) {                 // stays in the local grid (own or ghost column)
-        const uint32_t c = (gi - g.col_off) * g.rows + gj;
-        const uint32_t a = cell_count_fetch_inc(cell_count, c);
-        slot_cell[t] = c; arrival[t] = a;
-        if (a >= 255u) atomicOr(&ds->flags, FLAG_CELL_OVERFLOW);
-    } else {
-        slot_cell[t] = SLAB_INVALID;
+#pragma unroll
+    for (int j = 0; j < SORT_ILP; ++j) if (c[j] != SLAB_INVALID) a[j] = cell_count_fetch_inc(cell_count, c[j]);
+#pragma unroll
+    for (int j = 0; j < SORT_ILP; ++j) {
+        const uint32_t t = t0 + j * blockDim.x;
+        if (t >= n_own_prev) continue;
+        slot_cell[t] = c[j];
+        if (c[j] != SLAB_INVALID) {
+            arrival[t] = a[j];
+            if (a[j] >= 255u) atomicOr(&ds->flags, FLAG_CELL_OVERFLOW);
+        }
     }
 }
 
@@ -615,7 +631,7 @@ struct SlabCollider {
         PS_CUDA_TRY(err, cudaMemsetAsync(cell_count, 0, cell_count_bytes(ncell_local), st));
         slab_begin_kernel<Real><<<1, 32, 0, st>>>(sd, ds, send_l, send_r);
         own_b_step = last.own_b; n_own_step = last.own_e - last.own_b;   // the layout left by the previous sub-step (host copy)
-        slab_bin_kernel<Real><<<(n_own_step + 255) / 256 + 1, 256, 0, st>>>(rec[cur], pid[cur], own_b_step, n_own_step, k_step, g, cell_count, slot_cell, arrival, send_l, send_r, sd, ds);
+        slab_bin_kernel<Real><<<(n_own_step + 256 * SORT_ILP - 1) / (256 * SORT_ILP) + 1, 256, 0, st>>>(rec[cur], pid[cur], own_b_step, n_own_step, k_step, g, cell_count, slot_cell, arrival, send_l, send_r, sd, ds);
         launches += 2;
         PS_CUDA_TRY(err, cudaGetLastError());
         return PS_OK;
