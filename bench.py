@@ -408,6 +408,20 @@ def run_extras(torch, sim, scene, hp, hv, n, S, prec):
             out[f"integrate_{other}"] = {"value": n * S * 20 / (ms * 1e-3), "unit": UNIT, "hbm_gbs": gbs}
     except Exception as e:
         out[f"integrate_{other}"] = {"error": str(e)}
+    # the same end-to-end frame with f32 host buffers (ps_frame_host_f32): half the bytes over the host link
+    try:
+        h32 = [torch.empty((n, 2), dtype=torch.float32, pin_memory=True) for _ in range(3)]
+        a32 = [t.numpy() for t in h32]
+        a32[0][...] = hp
+        a32[1][...] = hv
+        timed(torch, None, lambda: sim.frame_host(a32[0], a32[1], a32[2], None, 1), 2)
+        ms = timed(torch, None, lambda: sim.frame_host(a32[0], a32[1], a32[2], None, 1), 5)
+        out["e2e_f32_host"] = {"value": n * S * 5 / (ms * 1e-3), "unit": UNIT, "ms_per_step": ms / 5,
+                               "h2d_bytes_per_step": int(a32[0].nbytes + a32[1].nbytes), "d2h_bytes_per_step": int(a32[2].nbytes),
+                               "note": "ps_frame_host_f32: a host that keeps f32 arrays; the headline e2e uses core.zig's f64 layout"}
+        del h32, a32
+    except Exception as e:
+        out["e2e_f32_host"] = {"error": str(e)}
     try:
         nc = 16 << 20
         cs = scenes.scaled_scene(nc)

@@ -6,6 +6,7 @@
 #include <cuda_runtime.h>
 
 #include <cstring>
+#include <exception>
 #include <memory>
 #include <mutex>
 #include <new>
@@ -505,7 +506,9 @@ int ps_create(const ps_config* cfg, ps_sim** out) {
         return PS_ERR_NO_DEVICE;
     }
     if (cfg->device < 0 || cfg->device >= ndev) { g_create_error = "ps_create: device ordinal out of range"; return PS_ERR_BAD_ARG; }
-    return cfg->precision == PS_F64 ? create_t<double>(cfg, rows, cols, out) : create_t<float>(cfg, rows, cols, out);
+    try {   // no C++ exception may cross the C boundary
+        return cfg->precision == PS_F64 ? create_t<double>(cfg, rows, cols, out) : create_t<float>(cfg, rows, cols, out);
+    } catch (const std::exception& ex) { g_create_error = std::string("ps_create: ") + ex.what(); return PS_ERR_OOM; }
 }
 
 void ps_destroy(ps_sim* sim) { delete sim; }
@@ -724,8 +727,10 @@ int ps_slab_create(const ps_config* cfg, int rank, int nranks, const void* nccl_
     const cudaError_t e = cudaGetDeviceCount(&ndev);
     if (e != cudaSuccess || ndev == 0) { cudaGetLastError(); g_create_error = "ps_slab_create: no CUDA device; this library has no CPU path"; return PS_ERR_NO_DEVICE; }
     if (cfg->device < 0 || cfg->device >= ndev) { g_create_error = "ps_slab_create: device ordinal out of range"; return PS_ERR_BAD_ARG; }
-    return cfg->precision == PS_F64 ? slab_create_t<double>(cfg, rank, nranks, nccl_id128, rows, cols, out)
-                                    : slab_create_t<float>(cfg, rank, nranks, nccl_id128, rows, cols, out);
+    try {
+        return cfg->precision == PS_F64 ? slab_create_t<double>(cfg, rank, nranks, nccl_id128, rows, cols, out)
+                                        : slab_create_t<float>(cfg, rank, nranks, nccl_id128, rows, cols, out);
+    } catch (const std::exception& ex) { g_create_error = std::string("ps_slab_create: ") + ex.what(); return PS_ERR_OOM; }
 }
 void ps_slab_destroy(ps_slab* s) { delete s; }
 int ps_slab_upload_global(ps_slab* s, const double* pos, const double* vel) { return (s && pos && vel) ? s->upload_global(pos, vel) : PS_ERR_BAD_ARG; }
@@ -818,7 +823,9 @@ int ps_slabgroup_create(const ps_config* cfg, int nranks, ps_slabgroup** out) {
     const cudaError_t e = cudaGetDeviceCount(&ndev);
     if (e != cudaSuccess || ndev == 0) { cudaGetLastError(); g_create_error = "ps_slabgroup_create: no CUDA device; this library has no CPU path"; return PS_ERR_NO_DEVICE; }
     if (cfg->device < 0 || cfg->device >= ndev) { g_create_error = "ps_slabgroup_create: device ordinal out of range"; return PS_ERR_BAD_ARG; }
-    return cfg->precision == PS_F64 ? slabgroup_create_t<double>(cfg, nranks, rows, cols, out) : slabgroup_create_t<float>(cfg, nranks, rows, cols, out);
+    try {
+        return cfg->precision == PS_F64 ? slabgroup_create_t<double>(cfg, nranks, rows, cols, out) : slabgroup_create_t<float>(cfg, nranks, rows, cols, out);
+    } catch (const std::exception& ex) { g_create_error = std::string("ps_slabgroup_create: ") + ex.what(); return PS_ERR_OOM; }
 }
 void ps_slabgroup_destroy(ps_slabgroup* g) { delete g; }
 int ps_slabgroup_upload_global(ps_slabgroup* g, const double* pos, const double* vel) { return (g && pos && vel) ? g->upload_global(pos, vel) : PS_ERR_BAD_ARG; }
