@@ -48,6 +48,7 @@ def parse_args():
     ap.add_argument("--variant", type=int, default=0, help="integrate kernel variant (0 = auto)")
     ap.add_argument("--sweep", action="store_true", help="time every integrate kernel variant and print a table to stderr")
     ap.add_argument("--ref-sample", type=int, default=4 << 20, help="particles per step of the CPU reference arm")
+    ap.add_argument("--ref-threads", type=int, default=0, help="host threads of the CPU reference arm (0 = all this process may use)")
     ap.add_argument("--workload", default="integrate", choices=["integrate", "collide"],
                     help="integrate = BASELINE.json configs[2] (default, the headline); collide = configs[4]: ONE 256 Mi-particle "
                          "collision scene slab-decomposed over the ranks (strong scaling)")
@@ -90,27 +91,48 @@ def spawn_chunked(scene, seed, start, count, dtype, out_pos, out_vel):
 # ------------------------------------------------------------------------------------------------
 # CPU reference arm / cpu_baseline: the C++ restatement of core.zig (oracle/), single thread.
 # ------------------------------------------------------------------------------------------------
-def cpu_reference_rate(scene, n_sample, frames, warm_frames=0, dtype=np.float64, seed=1):
-    """updates/s of the oracle port on `n_sample` particles, `frames` updatePhysics frames (integrate + bounce)."""
+def cpu_reference_rate(scene, n_sample, frames, warm_frames=0, dtype=np.float64, seed=1, threads=1):
+    """updates/s of the oracle port on `n_sample` particles, `frames` updatePhysics frames (integrate + bounce).
+
+    core.zig is single-threaded.  With threads > 1 the particle range is cut into that many contiguous slices and the
+    same port runs on every slice at once (integration-only particles are independent, so the result is the same);
+    the rate is then taken from the host clock around all slices."""
     import oracle  # the only place bench.py touches oracle/: as the timed CPU baseline, never as the product
-    from particle_simulator_b200 import scenes
+    from concurrent.futures import ThreadPoolExecutor
 
     sub = scene.with_(count=n_sample)
     pos = np.empty((n_sample, 2), dtype=dtype)
     vel = np.empty((n_sample, 2), dtype=dtype)
     spawn_chunked(scene, seed, 0, n_sample, dtype, pos, vel)
-    params = oracle.make_params(radius=sub.radius, width=sub.width, height=sub.height, grid_size=sub.grid_size,
+    # integration never touches the grid, but the port allocates it at init as SpatialHashGrid.init does (9 B per cell,
+    # over a gigabyte for this world, once per call): one whole-world cell keeps that out of every slice
+    params = oracle.make_params(radius=sub.radius, width=sub.width, height=sub.height, grid_size=max(sub.width, sub.height),
                                 target_fps=sub.target_fps, sub_steps=sub.sub_steps, g=sub.g,
                                 boundary_damping=sub.boundary_damping, particle_damping=sub.particle_damping)
     acc = np.zeros_like(pos)
+    threads = max(1, min(int(threads), n_sample or 1))
+    cuts = [n_sample * t // threads for t in range(threads + 1)]
+    pool = ThreadPoolExecutor(threads) if threads > 1 else None
+
+    def frame_run(substeps):
+        if pool is None:
+            return oracle.run(params, pos, vel, substeps, collisions=False, acc=acc)["seconds"]
+        t0 = time.perf_counter()          # ctypes drops the GIL inside the call: the slices really run side by side
+        list(pool.map(lambda t: oracle.run(params, pos[cuts[t]:cuts[t + 1]], vel[cuts[t]:cuts[t + 1]], substeps,
+                                           collisions=False, acc=acc[cuts[t]:cuts[t + 1]]), range(threads)))
+        return time.perf_counter() - t0
+
     if warm_frames:
-        oracle.run(params, pos, vel, warm_frames * sub.sub_steps, collisions=False, acc=acc)
-    secs = []
-    for _ in range(frames):
-        out = oracle.run(params, pos, vel, sub.sub_steps, collisions=False, acc=acc)
-        secs.append(out["seconds"])
+        frame_run(warm_frames * sub.sub_steps)
+    secs = [frame_run(sub.sub_steps) for _ in range(frames)]
+    if pool is not None:
+        pool.shutdown()
     total = float(sum(secs))
     return n_sample * sub.sub_steps * frames / total, total, secs
+
+
+ALL_THREADS_NOTE = ("not the reference (BASELINE.md B5): core.zig is single-threaded; the same port with the particle range cut into "
+                    "one contiguous slice per host thread, all slices running side by side")
 
 
 def run_reference(args):
@@ -124,6 +146,8 @@ def run_reference(args):
     n_sample = min(args.ref_sample, args.particles)
     rate, total, secs = cpu_reference_rate(scene, n_sample, args.steps, warm_frames=args.warmup, dtype=np.float64)
     ms = 1e3 * total / max(args.steps, 1)
+    threads = args.ref_threads if args.ref_threads > 0 else (len(os.sched_getaffinity(0)) or 1)
+    many, _, _ = cpu_reference_rate(scene, n_sample, max(1, min(args.steps, 10)), warm_frames=1, dtype=np.float64, threads=threads)
     sample = (f"{n_sample} of the {args.particles} particles per step, one updatePhysics frame (8 sub-steps, integrate + "
               f"wall bounce, f64 as core.zig is written), single thread (core.zig has no threads)")
     line = {
@@ -133,7 +157,8 @@ def run_reference(args):
         "data": "synthetic",
         "config": workload_config(args, "f64"),
         "cpu_baseline": {"value": rate, "unit": UNIT, "cores": 1, "kind": "port", "sample": sample,
-                         "host_cpus": os.cpu_count(), "host_cpu_model": host_cpu_model()},
+                         "host_cpus": os.cpu_count(), "host_cpu_model": host_cpu_model(),
+                         "all_host_threads": {"value": many, "cores": threads, "note": ALL_THREADS_NOTE}},
         "e2e": {"value": rate, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "note": "Zig toolchain absent: the reference arm is oracle/core_ref.hpp, a C++ restatement of src/core.zig "
                 "(g++ -O2 -ffp-contract=off); parity with the Zig binary is unpinned",
@@ -351,9 +376,12 @@ def run_ours(args):
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         n_s = min(n, 16 << 20)
         rate, total, _ = cpu_reference_rate(scene_all, n_s, frames=4, warm_frames=0, dtype=np.float64)
+        threads = args.ref_threads if args.ref_threads > 0 else (len(os.sched_getaffinity(0)) or 1)
+        many, total_m, _ = cpu_reference_rate(scene_all, n_s, frames=8, warm_frames=1, dtype=np.float64, threads=threads)
         cpu = {"value": rate, "unit": UNIT, "cores": 1, "kind": "port", "host_cpus": os.cpu_count(), "host_cpu_model": host_cpu_model(),
                "sample": f"{n_s} of the {n} particles, 4 updatePhysics frames (32 sub-steps) of integrate + wall bounce in f64 "
-                         f"(core.zig as written), oracle/core_ref.hpp single thread, {total:.1f} s of CPU work"}
+                         f"(core.zig as written), oracle/core_ref.hpp single thread, {total:.1f} s of CPU work",
+               "all_host_threads": {"value": many, "cores": threads, "note": ALL_THREADS_NOTE}}
 
     if dist is not None:
         dist.barrier()
