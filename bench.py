@@ -374,14 +374,20 @@ def run_ours(args):
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        # timed in a fresh process: the same code as `--impl reference`, away from this process's CUDA context, pinned
+        # buffers and helper threads
+        import subprocess
+
         n_s = min(n, 16 << 20)
-        rate, total, _ = cpu_reference_rate(scene_all, n_s, frames=4, warm_frames=0, dtype=np.float64)
-        threads = args.ref_threads if args.ref_threads > 0 else (len(os.sched_getaffinity(0)) or 1)
-        many, total_m, _ = cpu_reference_rate(scene_all, n_s, frames=8, warm_frames=1, dtype=np.float64, threads=threads)
-        cpu = {"value": rate, "unit": UNIT, "cores": 1, "kind": "port", "host_cpus": os.cpu_count(), "host_cpu_model": host_cpu_model(),
-               "sample": f"{n_s} of the {n} particles, 4 updatePhysics frames (32 sub-steps) of integrate + wall bounce in f64 "
-                         f"(core.zig as written), oracle/core_ref.hpp single thread, {total:.1f} s of CPU work",
-               "all_host_threads": {"value": many, "cores": threads, "note": ALL_THREADS_NOTE}}
+        cmd = [sys.executable, os.path.abspath(__file__), "--impl", "reference", "--particles", str(n), "--ref-sample", str(n_s),
+               "--steps", "4", "--warmup", "1", "--ref-threads", str(args.ref_threads)]
+        try:
+            res = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+            cpu = json.loads(res.stdout.strip().splitlines()[-1])["cpu_baseline"]
+            cpu["sample"] = (f"{n_s} of the {n} particles, 4 updatePhysics frames (32 sub-steps) of integrate + wall bounce in f64 "
+                             f"(core.zig as written), oracle/core_ref.hpp single thread, own process")
+        except Exception as e:  # noqa: BLE001
+            cpu = {"error": f"CPU baseline failed: {e}"}
 
     if dist is not None:
         dist.barrier()
@@ -467,28 +473,34 @@ def run_extras(torch, sim, scene, hp, hv, n, S, prec):
                                        "note": "BASELINE.json configs[3]: full updatePhysics with exact-order resolve"}
     except Exception as e:
         out["collide_16Mi_f32"] = {"error": str(e)}
-    # the faithful updatePhysics (collisions on, f64) on the CPU port, and the same scenes on the GPU
+    # BASELINE.md section 3, runs B1-B4: the CPU port (f64 unless noted, one thread) beside the same scene on the GPU
     try:
         import oracle
 
-        for name, cs, substeps in (("default_13k", scenes.default_scene(), 1000), ("1Mi", scenes.scaled_scene(1 << 20), 24)):
-            pos, vel = scenes.spawn(cs, seed=1)
+        d13, m1 = scenes.default_scene(), scenes.scaled_scene(1 << 20)
+        plan = (("B1", "collide_default_13k_f64", d13, 1000, True, "f64"), ("B2", "integrate_default_13k_f64", d13, 1000, False, "f64"),
+                ("B3", "integrate_1Mi_f64", m1, 1000, False, "f64"), ("B3", "integrate_1Mi_f32", m1, 1000, False, "f32"),
+                ("B4", "collide_1Mi_f64", m1, 24, True, "f64"))
+        for tag, name, cs, substeps, coll, pr in plan:
+            pos, vel = scenes.spawn(cs, seed=1, dtype=np.float64 if pr == "f64" else np.float32)
             params = oracle.make_params(radius=cs.radius, width=cs.width, height=cs.height, grid_size=cs.grid_size)
             p, v = pos.copy(), vel.copy()
-            secs = oracle.run(params, p, v, substeps, collisions=True)["seconds"]
-            with Simulation(cs, precision="f64", collisions=True) as c:
+            secs = oracle.run(params, p, v, substeps, collisions=coll)["seconds"]
+            with Simulation(cs, precision=pr, collisions=coll) as c:
                 c.set_stream(stream)
                 c.upload(pos, vel)
                 c.step_substeps(8)
                 c.upload(pos, vel)
                 ms = timed(torch, None, lambda: c.step_substeps(substeps), 1)
-                gp, gv = c.download()
-            out[f"collide_{name}_f64"] = {"cpu_port_updates_per_s": cs.count * substeps / secs, "gpu_updates_per_s": cs.count * substeps / (ms * 1e-3),
-                                          "substeps": substeps, "bit_identical": bool(np.array_equal(gp.view(np.uint8), p.view(np.uint8)) and
-                                                                                      np.array_equal(gv.view(np.uint8), v.view(np.uint8))),
-                                          "note": "full updatePhysics with collisions, f64: oracle/core_ref.hpp single thread vs libparticles_cuda (device-resident)"}
+                gp, gv = c.download(dtype=pos.dtype)
+            out[name] = {"plan": tag, "cpu_port_updates_per_s": cs.count * substeps / secs, "cpu_wall_s": secs,
+                         "gpu_updates_per_s": cs.count * substeps / (ms * 1e-3), "gpu_wall_s": ms * 1e-3, "substeps": substeps,
+                         "bit_identical": bool(np.array_equal(gp.view(np.uint8), p.view(np.uint8)) and
+                                               np.array_equal(gv.view(np.uint8), v.view(np.uint8))),
+                         "note": ("full updatePhysics with collisions" if coll else "integrate + wall bounce only") +
+                                 f", {pr}: oracle/core_ref.hpp single thread vs libparticles_cuda (device-resident)"}
     except Exception as e:
-        out["collide_cpu_compare"] = {"error": str(e)}
+        out["cpu_compare"] = {"error": str(e)}
     return out
 
 
