@@ -1,7 +1,8 @@
 #!/usr/bin/env python
 """Turn ncu outputs brought back in gpurun_out/ into the small text summaries kept under profiles/.
 
-    python tools/ncu_summary.py launches <launches.csv> <out.md>          # per-kernel totals and shares of a launch list
+    python tools/ncu_summary.py launches <launches.csv> <out.md> [--particles N --cells C --pairs P [--peak GBps]]
+                                                  # per-kernel totals and shares of a launch list (+ GB/s per kernel)
     python tools/ncu_summary.py full <report.ncu-rep> <out.csv> [--traffic-json profiles/roofline_traffic.json]
 """
 import collections
@@ -28,7 +29,7 @@ KEEP = [
 BYTES = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12}
 
 
-def launches(path, out):
+def launches(path, out, algo=None):
     with open(path) as fh:
         lines = [l for l in fh if not l.startswith("==")]
     agg, cnt = collections.OrderedDict(), collections.Counter()
@@ -48,6 +49,23 @@ def launches(path, out):
         f.write("| kernel | launches | total ms | avg ms | share |\n|---|---:|---:|---:|---:|\n")
         for k, v in sorted(agg.items(), key=lambda x: -x[1]):
             f.write(f"| `{k}` | {cnt[k]} | {v:.3f} | {v / cnt[k]:.4f} | {100 * v / tot:.1f}% |\n")
+        if algo:
+            # algorithmic bytes of the collision kernels (fp32 records), DESIGN.md section 4: per particle, per cell or per listed pair
+            per = {"bin_kernel": ("particle", 24), "place_kernel": ("particle", 16), "move_kernel": ("particle", 48),
+                   "scan_reduce_kernel": ("cell", 1), "scan_down_kernel": ("cell", 5), "detect_kernel": ("particle", 28),
+                   "resolve_kernel": ("pair", 100), "integrate_bounce_kernel": ("particle", 32)}
+            f.write(f"\nPer kernel against the HBM roofline ({algo['particles']} particles, {algo['cells']} cells, {algo['pairs']} listed pairs; "
+                    f"peak {algo['peak']} GB/s measured copy bandwidth):\n\n")
+            f.write("| kernel | avg ms | particles/s | algorithmic bytes per launch | GB/s | of peak |\n|---|---:|---:|---:|---:|---:|\n")
+            for k, v in sorted(agg.items(), key=lambda x: -x[1]):
+                base = k.split("<")[0]
+                if base not in per:
+                    continue
+                unit, nbytes = per[base]
+                ms = v / cnt[k]
+                total = nbytes * algo[{"particle": "particles", "cell": "cells", "pair": "pairs"}[unit]]
+                gbs = total / (ms * 1e-3) / 1e9
+                f.write(f"| `{k}` | {ms:.4f} | {algo['particles'] / (ms * 1e-3):.3g} | {total / 1e6:.0f} MB ({nbytes} B per {unit}) | {gbs:.0f} | {100 * gbs / algo['peak']:.0f}% |\n")
     print(open(out).read())
 
 
@@ -84,7 +102,13 @@ def full(rep, out, traffic_json=None):
 
 if __name__ == "__main__":
     if sys.argv[1] == "launches":
-        launches(sys.argv[2], sys.argv[3])
+        algo = None
+        if "--particles" in sys.argv:
+            def opt(name, default):
+                return float(sys.argv[sys.argv.index(name) + 1]) if name in sys.argv else default
+            algo = {"particles": int(opt("--particles", 0)), "cells": int(opt("--cells", 0)), "pairs": int(opt("--pairs", 0)),
+                    "peak": opt("--peak", 6442.6)}
+        launches(sys.argv[2], sys.argv[3], algo)
     else:
         tj = sys.argv[sys.argv.index("--traffic-json") + 1] if "--traffic-json" in sys.argv else None
         full(sys.argv[2], sys.argv[3], tj)
