@@ -107,9 +107,12 @@ struct DevState {
 __device__ __forceinline__ unsigned long long global_ns() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
 constexpr uint32_t FLAG_CELL_OVERFLOW = 1u, FLAG_CAPACITY = 2u, FLAG_CORRUPT = 4u;
 
-// contact-list entry: partner slot (28 bits) | offset index (3 bits) | role (1 = this particle is the centre)
+// contact-list entry: partner slot (28 bits) | role (bit 31: 1 = this particle is the centre).  The offset index is not
+// stored: a partner from another cell appears once in a sub-list, a partner from the own cell twice with opposite roles
+// (SURVEY Q1), so partner + role identify the entry.
 constexpr uint32_t ENT_SLOT_MASK = (1u << 28) - 1;
-__device__ __forceinline__ uint32_t make_entry(uint32_t partner, uint32_t o, uint32_t centre) { return partner | (o << 28) | (centre << 31); }
+constexpr uint32_t ENT_CENTRE = 1u << 31;
+__device__ __forceinline__ uint32_t make_entry(uint32_t partner, uint32_t /*o*/, uint32_t centre) { return partner | (centre << 31); }
 
 // x / grid_size (src/core.zig:104-105).  When grid_size is a power of two (the reference's 4.0) the quotient equals
 // x * (1 / grid_size) bit for bit (scaling by a power of two is exact), which spares the IEEE division sequence.
@@ -118,14 +121,21 @@ __device__ __forceinline__ Real cell_coord(Real x, const StepConst<Real>& k) {
     return k.gs_pow2 ? x * k.inv_gs : div_rn(x, k.grid_size);
 }
 
-// computeCoordinate + computeGridIndex (src/core.zig:103-121)
+// computeCoordinate (src/core.zig:103-117): column i and row j of the cell
 template <class Real>
-__device__ __forceinline__ uint32_t cell_of(Real x, Real y, const StepConst<Real>& k) {
+__device__ __forceinline__ void cell_xy(Real x, Real y, const StepConst<Real>& k, uint32_t& i, uint32_t& j) {
     const Real fi = floor_r(cell_coord<Real>(x, k));
     const Real fj = floor_r(cell_coord<Real>(y, k));
     // positions are inside [r, dim-r] here; the clamp mirrors @min(i, cols-1) and guards NaN / negatives
-    uint32_t i = fi > (Real)0 ? (fi < (Real)k.cols ? (uint32_t)fi : k.cols - 1) : 0u;
-    uint32_t j = fj > (Real)0 ? (fj < (Real)k.rows ? (uint32_t)fj : k.rows - 1) : 0u;
+    i = fi > (Real)0 ? (fi < (Real)k.cols ? (uint32_t)fi : k.cols - 1) : 0u;
+    j = fj > (Real)0 ? (fj < (Real)k.rows ? (uint32_t)fj : k.rows - 1) : 0u;
+}
+
+// computeCoordinate + computeGridIndex (src/core.zig:103-121)
+template <class Real>
+__device__ __forceinline__ uint32_t cell_of(Real x, Real y, const StepConst<Real>& k) {
+    uint32_t i, j;
+    cell_xy<Real>(x, y, k, i, j);
     return i * k.rows + j;
 }
 
@@ -265,10 +275,14 @@ struct Stencil {   // slot ranges of the 3x3 block around one cell, loaded once 
 };
 
 template <class Real>
-__device__ __forceinline__ Stencil load_stencil(const uint32_t* __restrict__ cell_start, uint32_t c, const StepConst<Real>& k) {
+__device__ __forceinline__ Stencil load_stencil(const uint32_t* __restrict__ cell_start, uint32_t c, const StepConst<Real>& k);   // by cell index, below
+
+template <class Real>
+__device__ __forceinline__ Stencil load_stencil(const uint32_t* __restrict__ cell_start, uint32_t gx, uint32_t gy, uint32_t ncols,
+                                                const StepConst<Real>& k) {
     Stencil s{};
-    const uint32_t rows = k.rows, cols = k.cols;
-    const uint32_t gx = c / rows, gy = c - gx * rows;
+    const uint32_t rows = k.rows, cols = ncols;
+    const uint32_t c = gx * rows + gy;
     s.up = gy > 0; s.down = gy + 1 < rows; s.left = gx > 0; s.right = gx + 1 < cols;
     s.m1 = cell_start[c]; s.m2 = cell_start[c + 1];
     s.m0 = s.up ? cell_start[c - 1] : s.m1;
@@ -286,6 +300,12 @@ __device__ __forceinline__ Stencil load_stencil(const uint32_t* __restrict__ cel
         s.r3 = s.down ? cell_start[cr + 2] : s.r2;
     }
     return s;
+}
+
+template <class Real>
+__device__ __forceinline__ Stencil load_stencil(const uint32_t* __restrict__ cell_start, uint32_t c, const StepConst<Real>& k) {
+    const uint32_t gx = c / k.rows;
+    return load_stencil<Real>(cell_start, gx, c - gx * k.rows, k.cols, k);
 }
 
 template <class Real, class F>
@@ -440,6 +460,83 @@ __device__ __forceinline__ uint32_t emit_block(M mask, const Stencil& st, uint32
     return w;
 }
 
+// ---- the usual case: at most 31 candidates ------------------------------------------------------------------
+// One flat loop tests the candidates of all three columns (iterations per warp = the largest block among its lanes,
+// not the sum of the largest columns); bit t of the result = t-th candidate in column order (left, own, right).
+template <class Real>
+__device__ __forceinline__ uint32_t test_flat(const Rec<Real>* __restrict__ rec, uint32_t a, decltype(ld_pos((const Rec<Real>*)nullptr)) pa,
+                                              const Stencil& st, uint32_t nL, uint32_t nM, uint32_t total, Real r2sq) {
+    const uint32_t bL = st.l0, bM = st.m0 - nL, bR = st.r0 - nL - nM, nLM = nL + nM;   // wrap-around arithmetic: slot = base + t
+    uint32_t hits = 0;
+#pragma unroll 2
+    for (uint32_t t = 0; t < total; ++t) {
+        const uint32_t q = t + (t < nL ? bL : (t < nLM ? bM : bR));
+        const auto pq = ld_pos(rec + q);
+        const Real dx = pq.x - pa.x, dy = pq.y - pa.y;      // (xj-xi)^2 does not depend on which of the two is i (:333-338)
+        const Real d2 = dx * dx + dy * dy;
+        hits |= (d2 < r2sq ? 1u : 0u) << t;
+    }
+    return hits & ~(1u << (nL + (a - st.m0)));              // pi != pj (:199)
+}
+
+// The sub-list of slot `a` as eight runs of consecutive slots, in list order (the eleven segments documented at
+// walk_contacts; neighbouring segments that are contiguous in slot space and share the role are one run):
+//   0 [l0,l2) neighbour   1 [m0,a) neighbour   2 [m1,a) centre    3 (a,m3) centre
+//   4 [r1,r3) centre      5 [l2,l3) centre     6 (a,m2) neighbour 7 [r0,r1) neighbour
+// ListRuns holds where each run starts in "list space" (bit position in the list-ordered mask).
+struct ListRuns {
+    uint32_t t1, t2, t3, t4, t5, t6, t7, t8;               // start of runs 1..7 and the total length (run 0 starts at 0)
+};
+__device__ __forceinline__ ListRuns list_runs(const Stencil& st, uint32_t a) {
+    ListRuns r;
+    r.t1 = st.l2 - st.l0;
+    r.t2 = r.t1 + (a - st.m0);
+    r.t3 = r.t2 + (a - st.m1);
+    r.t4 = r.t3 + (st.m3 - a - 1u);
+    r.t5 = r.t4 + (st.r3 - st.r1);
+    r.t6 = r.t5 + (st.l3 - st.l2);
+    r.t7 = r.t6 + (st.m2 - a - 1u);
+    r.t8 = r.t7 + (st.r1 - st.r0);
+    return r;
+}
+
+// Reorder the column-ordered hit mask into list order (own-cell partners appear twice, Q1).  All shifts are < 32 and all
+// lengths <= 31 because the caller takes this path only when r.t8 <= 31.  `own` drops the runs whose centre lies in a
+// column of another rank (multi-GPU slabs).
+__device__ __forceinline__ uint32_t list_mask(uint32_t hits, const Stencil& st, uint32_t a, uint32_t nL, uint32_t nM,
+                                              const ListRuns& r, OwnFlags own) {
+    auto run = [&](uint32_t src, uint32_t len, uint32_t dst) { return ((hits >> src) & ((1u << len) - 1u)) << dst; };
+    const uint32_t am = nL + (a - st.m0);                   // bit of `a` itself in column order
+    uint32_t left = run(0u, r.t1, 0u);
+    uint32_t mid = run(nL, r.t2 - r.t1, r.t1) | run(nL + (st.m1 - st.m0), r.t3 - r.t2, r.t2) | run(am + 1u, r.t4 - r.t3, r.t3) |
+                   run(nL + nM + (st.r1 - st.r0), r.t5 - r.t4, r.t4) | run(r.t1, r.t6 - r.t5, r.t5) | run(am + 1u, r.t7 - r.t6, r.t6);
+    uint32_t right = run(nL + nM, r.t8 - r.t7, r.t7);
+    if (!own.l_own) left = 0u;
+    if (!own.a_own) mid = 0u;
+    if (!own.r_own) right = 0u;
+    return left | mid | right;
+}
+
+// Write the entries of a list-ordered mask; returns the first one.  Entry of list bit p in run i = base_i + p with
+// base_i = (first slot of the run - start of the run) + role bit, all modulo 2^32.
+__device__ __forceinline__ uint32_t emit_list(uint32_t lm, const Stencil& st, uint32_t a, const ListRuns& r,
+                                              uint32_t* __restrict__ entries, uint32_t w) {
+    const uint32_t b0 = st.l0, b1 = st.m0 - r.t1, b2 = st.m1 - r.t2 + ENT_CENTRE, b3 = a + 1u - r.t3 + ENT_CENTRE,
+                   b4 = st.r1 - r.t4 + ENT_CENTRE, b5 = st.l2 - r.t5 + ENT_CENTRE, b6 = a + 1u - r.t6, b7 = st.r0 - r.t7;
+    uint32_t first = 0u;
+    bool have = false;
+    while (lm) {
+        const uint32_t p = (uint32_t)__ffs((int)lm) - 1u;
+        lm &= lm - 1u;
+        const uint32_t lo = p < r.t2 ? (p < r.t1 ? b0 : b1) : (p < r.t3 ? b2 : b3);
+        const uint32_t hi = p < r.t6 ? (p < r.t5 ? b4 : b5) : (p < r.t7 ? b6 : b7);
+        const uint32_t e = (p < r.t4 ? lo : hi) + p;
+        entries[w++] = e;
+        if (!have) { first = e; have = true; }
+    }
+    return first;
+}
+
 template <class Real, bool SLAB>
 __global__ void __launch_bounds__(256, sizeof(Real) == 4 ? 6 : 4)   // 40 / 64 registers: more resident warps to hide the load latency
 detect_kernel(const Rec<Real>* __restrict__ rec, const uint32_t* __restrict__ cell_start, uint32_t n, StepConst<Real> k,
@@ -464,34 +561,35 @@ detect_kernel(const Rec<Real>* __restrict__ rec, const uint32_t* __restrict__ ce
     OwnFlags own{true, true, true};
     bool blocked = false;
     if (valid) {
-        uint32_t c;
         if (SLAB) {
             // local cell: global computeCoordinate, then shift by the slab's first local column
             const Real fi = floor_r(cell_coord<Real>(pa.x, k)), fj = floor_r(cell_coord<Real>(pa.y, k));
             const uint32_t gi = fi > (Real)0 ? (fi < (Real)sv.gcols ? (uint32_t)fi : sv.gcols - 1) : 0u;
-            const uint32_t gj = fj > (Real)0 ? (fj < (Real)k.rows ? (uint32_t)fj : k.rows - 1) : 0u;
-            const uint32_t lx = gi - sv.col_off;
-            c = lx * k.rows + gj;
+            uint32_t gj = fj > (Real)0 ? (fj < (Real)k.rows ? (uint32_t)fj : k.rows - 1) : 0u;
+            uint32_t lx = gi - sv.col_off;
             if (lx >= sv.ncl) {                                  // a record outside the local grid: corrupt state, stop before indexing with it
                 if (!atomicOr(&ds->flags, FLAG_CORRUPT)) { ds->dbg[0] = a; ds->dbg[1] = gi; ds->dbg[2] = gj; ds->dbg[3] = n; }
-                c = 0;
+                lx = 0; gj = 0;
             }
             own.a_own = lx >= sv.gl && lx < sv.ncl - sv.gr;
             own.l_own = lx >= 1u && (lx - 1u) >= sv.gl && (lx - 1u) < sv.ncl - sv.gr;
             own.r_own = (lx + 1u) >= sv.gl && (lx + 1u) < sv.ncl - sv.gr;
             blocked = a < *sv.n_blocked;
+            st = load_stencil<Real>(cell_start, lx, gj, k.cols, k);
         } else {
-            c = cell_of<Real>(pa.x, pa.y, k);
+            uint32_t gx, gy;
+            cell_xy<Real>(pa.x, pa.y, k, gx, gy);
+            st = load_stencil<Real>(cell_start, gx, gy, k.cols, k);
         }
-        st = load_stencil<Real>(cell_start, c, k);
-        nL = st.left ? st.l3 - st.l0 : 0u;
+        nL = st.l3 - st.l0;                                   // (all zero when the column does not exist)
         nM = st.m3 - st.m0;
-        const uint32_t nR = st.right ? st.r3 - st.r0 : 0u;
-        const uint32_t total = nL + nM + nR;
-        path = total <= 32u ? 0 : (total <= 64u ? 1 : 2);
+        const uint32_t total = nL + nM + (st.r3 - st.r0);
+        // list length bound: every candidate once, own-cell partners twice
+        path = total + (st.m2 - st.m1) <= 32u ? 0 : (total <= 64u ? 1 : 2);
         if (path == 0) {
-            m32 = test_block<Real, uint32_t>(rec, a, pa, st, k.r2sq);
-            cnt = count_block<uint32_t, SLAB>(m32, st, nL, nM, own);
+            const uint32_t hits = test_flat<Real>(rec, a, pa, st, nL, nM, total, k.r2sq);
+            m32 = list_mask(hits, st, a, nL, nM, list_runs(st, a), own);
+            cnt = (uint32_t)__popc(m32);
         } else if (path == 1) {
             m64 = test_block<Real, unsigned long long>(rec, a, pa, st, k.r2sq);
             cnt = count_block<unsigned long long, SLAB>(m64, st, nL, nM, own);
@@ -523,8 +621,9 @@ detect_kernel(const Rec<Real>* __restrict__ rec, const uint32_t* __restrict__ ce
     head[a] = head_word(0u, blocked ? 0u : cnt, begin);
     if (SLAB && blocked) sv.brem[a] = cnt;                   // brem is zero everywhere else (cleared at creation and by the unblock kernel)
     if (!cnt) return;
+    uint32_t first_entry;
     if (path == 0) {
-        emit_block<uint32_t>(m32, st, a, nL, nM, own, entries, begin);
+        first_entry = emit_list(m32, st, a, list_runs(st, a), entries, begin);
     } else if (path == 1) {
         emit_block<unsigned long long>(m64, st, a, nL, nM, own, entries, begin);
     } else {
@@ -534,7 +633,8 @@ detect_kernel(const Rec<Real>* __restrict__ rec, const uint32_t* __restrict__ ce
             if (keep) entries[w++] = make_entry(q, o, centre);
         });
     }
-    if (!blocked) wl0[sh_wbase + (ex >> 22)] = make_uint2(a, entries[begin]);
+    if (path != 0) first_entry = entries[begin];
+    if (!blocked) wl0[sh_wbase + (ex >> 22)] = make_uint2(a, first_entry);
 }
 
 
@@ -628,8 +728,8 @@ __device__ __forceinline__ int resolve_item(Rec<Real>* rec, const uint32_t* __re
     const uint32_t eb = entries[ib];
     const uint32_t ea_next = rem_a > 1 ? entries[ia + 1] : 0u;
     const uint32_t eb_next = rem_b > 1 ? entries[ib + 1] : 0u;
-    // same pair seen from the other side: partner = a, same offset, opposite role
-    if (eb != (a | (ea & (7u << 28)) | (~ea & (1u << 31)))) return 0;
+    // same pair seen from the other side: partner = a, opposite role
+    if (eb != (a | (~ea & ENT_CENTRE))) return 0;
     // Both particles on this round's list (b's head last moved in round r-1, or never when r = 0): the
     // lower slot runs the pair.  Membership is read from the SAME 64-bit word as the cursor, so a
     // concurrent executor cannot make the two threads disagree.
