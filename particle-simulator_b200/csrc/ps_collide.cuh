@@ -774,12 +774,55 @@ __device__ __forceinline__ void resolve_round(Rec<Real>* rec, const uint32_t* __
     }
 }
 
+// The same round for the grid phase, without any CTA barrier: every warp walks its share of the work list on its own
+// (the next item is requested one batch ahead), collects the items it produces in its own shared-memory buffer and
+// moves them to `out` with one global atomic per flush.  Warps therefore never wait for each other inside a round, and
+// the chain of dependent L2 round trips of one batch overlaps with those of the other warps' batches.
+constexpr uint32_t RESOLVE_WBUF = 128;   // items per warp buffer; a batch appends at most 64
+template <class Real>
+__device__ __forceinline__ void resolve_round_warps(Rec<Real>* rec, const uint32_t* __restrict__ entries, unsigned long long* head,
+                                                    const uint2* wl, uint32_t cnt, uint2* out, uint32_t* out_count, uint32_t r,
+                                                    uint32_t first, uint32_t stride, const StepConst<Real>& k, uint2* sh_wbuf) {
+    const uint32_t lane = threadIdx.x & 31u;
+    uint2* buf = sh_wbuf + (threadIdx.x >> 5) * RESOLVE_WBUF;
+    uint32_t held = 0;                                       // items in this warp's buffer (same value in every lane)
+    auto flush = [&]() {
+        uint32_t base = 0;
+        if (lane == 0) base = atomicAdd(out_count, held);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        __syncwarp();
+        for (uint32_t i = lane; i < held; i += 32u) out[base + i] = buf[i];
+        __syncwarp();
+        held = 0;
+    };
+    uint32_t idx = first + threadIdx.x;                      // `first` is a multiple of 32: a warp's lanes share the trip count
+    uint2 item = idx < cnt ? __ldcg(wl + idx) : make_uint2(0u, 0u);
+    for (; idx - lane < cnt; idx += stride) {
+        const bool live = idx < cnt;
+        const uint2 cur = item;
+        const uint32_t ahead = idx + stride;
+        if (ahead < cnt) item = __ldcg(wl + ahead);
+        uint2 next[2];
+        const int m = live ? resolve_item<Real, false>(rec, entries, head, cur, r, k, next) : 0;
+        const uint32_t one = __ballot_sync(0xffffffffu, m >= 1), two = __ballot_sync(0xffffffffu, m >= 2);
+        if (one) {
+            const uint32_t below = (1u << lane) - 1u;
+            const uint32_t at = held + (uint32_t)__popc(one & below) + (uint32_t)__popc(two & below);
+            if (m >= 1) buf[at] = next[0];
+            if (m >= 2) buf[at + 1] = next[1];
+            held += (uint32_t)__popc(one) + (uint32_t)__popc(two);
+            if (held > RESOLVE_WBUF - 64u) flush();
+        }
+    }
+    if (held) flush();
+}
+
 template <class Real>
 __global__ void __launch_bounds__(RESOLVE_THREADS)
 resolve_kernel(Rec<Real>* rec, const uint32_t* __restrict__ entries, unsigned long long* head,
                uint2* wl0, uint2* wl1, uint2* wl2, StepConst<Real> k, DevState* ds, uint32_t r_start) {
     cg::grid_group grid = cg::this_grid();
-    __shared__ uint2 sh_buf[2 * RESOLVE_THREADS];
+    __shared__ uint2 sh_buf[(RESOLVE_THREADS / 32) * RESOLVE_WBUF];   // grid phase: one append buffer per warp; tail: one for the CTA
     __shared__ uint32_t sh_cnt, sh_base;
     uint2* lists[3] = {wl0, wl1, wl2};
     const bool leader = blockIdx.x == 0 && threadIdx.x == 0;
@@ -797,8 +840,8 @@ resolve_kernel(Rec<Real>* rec, const uint32_t* __restrict__ entries, unsigned lo
         if (trace && r < 64) { ds->trace_cnt[r] = cnt; ds->trace_ns[r] = (uint32_t)(global_ns() - t_begin); }
         if (cnt <= RESOLVE_TAIL) break;                      // same value in every thread: the whole grid leaves together
         if (leader) ds->wl_count[nn] = 0;                    // consumed in round r-1, refilled in round r+1
-        resolve_round<Real>(rec, entries, head, lists[cur], cnt, lists[nxt], &ds->wl_count[nxt], r,
-                            blockIdx.x * RESOLVE_THREADS, gridDim.x * RESOLVE_THREADS, RESOLVE_THREADS, k, sh_buf, &sh_cnt, &sh_base);
+        resolve_round_warps<Real>(rec, entries, head, lists[cur], cnt, lists[nxt], &ds->wl_count[nxt], r,
+                                  blockIdx.x * RESOLVE_THREADS, gridDim.x * RESOLVE_THREADS, k, sh_buf);
         grid.sync();
     }
     if (blockIdx.x != 0 || threadIdx.x >= RESOLVE_TAIL_THREADS) return;     // exited threads count as arrived at later CTA barriers
