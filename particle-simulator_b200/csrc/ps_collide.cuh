@@ -460,6 +460,18 @@ __device__ __forceinline__ uint32_t emit_block(M mask, const Stencil& st, uint32
     return w;
 }
 
+#ifndef PS_DETECT_UNROLL
+#define PS_DETECT_UNROLL 2      // tuning knobs of detect_kernel.  Measured on B200 at 16 Mi particles, whole sub-step: unroll 1 / 4: +1.6 %;
+                                // 5 or 8 CTAs per SM (48 / 32 registers): +4 % / -1 %; 128- or 512-thread CTAs: +4 % / +3 %
+#endif
+#ifndef PS_DETECT_MINB
+#define PS_DETECT_MINB 6
+#endif
+#ifndef PS_DETECT_THREADS
+#define PS_DETECT_THREADS 256
+#endif
+constexpr int kDetectUnroll = PS_DETECT_UNROLL;
+constexpr int DETECT_THREADS = PS_DETECT_THREADS;   // CTA size of detect_kernel: the unit of list-space reservation (one scan + two atomics per CTA)
 // ---- the usual case: at most 31 candidates ------------------------------------------------------------------
 // One flat loop tests the candidates of all three columns (iterations per warp = the largest block among its lanes,
 // not the sum of the largest columns); bit t of the result = t-th candidate in column order (left, own, right).
@@ -468,7 +480,7 @@ __device__ __forceinline__ uint32_t test_flat(const Rec<Real>* __restrict__ rec,
                                               const Stencil& st, uint32_t nL, uint32_t nM, uint32_t total, Real r2sq) {
     const uint32_t bL = st.l0, bM = st.m0 - nL, bR = st.r0 - nL - nM, nLM = nL + nM;   // wrap-around arithmetic: slot = base + t
     uint32_t hits = 0;
-#pragma unroll 2
+#pragma unroll kDetectUnroll
     for (uint32_t t = 0; t < total; ++t) {
         const uint32_t q = t + (t < nL ? bL : (t < nLM ? bM : bR));
         const auto pq = ld_pos(rec + q);
@@ -538,7 +550,7 @@ __device__ __forceinline__ uint32_t emit_list(uint32_t lm, const Stencil& st, ui
 }
 
 template <class Real, bool SLAB>
-__global__ void __launch_bounds__(256, sizeof(Real) == 4 ? 6 : 4)   // 40 / 64 registers: more resident warps to hide the load latency
+__global__ void __launch_bounds__(DETECT_THREADS, (sizeof(Real) == 4 ? PS_DETECT_MINB : 4) * 256 / DETECT_THREADS)   // 40 / 64 registers: more resident warps to hide the load latency
 detect_kernel(const Rec<Real>* __restrict__ rec, const uint32_t* __restrict__ cell_start, uint32_t n, StepConst<Real> k,
               uint32_t* __restrict__ entries, uint32_t entries_cap, unsigned long long* __restrict__ head,
               uint2* __restrict__ wl0, DevState* __restrict__ ds, SlabView sv) {
@@ -603,7 +615,7 @@ detect_kernel(const Rec<Real>* __restrict__ rec, const uint32_t* __restrict__ ce
     // packed CTA scan: entry count in the low 22 bits, "goes on the first work list" flag above
     const uint32_t packed = cnt | (((cnt && !blocked) ? 1u : 0u) << 22);
     uint32_t total;
-    const uint32_t ex = block_exclusive_scan<256>(packed, &total);
+    const uint32_t ex = block_exclusive_scan<DETECT_THREADS>(packed, &total);
     if (threadIdx.x == 0) {
         const uint32_t te = total & ((1u << 22) - 1), tw = total >> 22;
         sh_base = te ? atomicAdd(&ds->entries_used, te) : 0u;
@@ -1017,7 +1029,7 @@ struct Collider {
         PS_CUDA_TRY(err, exclusive_scan<uint8_t>(reinterpret_cast<const uint8_t*>(cell_count), cell_start, ncell, scan_sums, cell_start + ncell, &ds->max_cell, st));
         place_kernel<<<(gn + SORT_ILP - 1) / SORT_ILP, 256, 0, st>>>(slot_cell, arrival, pid[cur], cell_start, n32, tmp_id);
         move_kernel<Real><<<(gn + SORT_ILP - 1) / SORT_ILP, 256, 0, st>>>(rec[cur], pid[cur], slot_cell, cell_start, tmp_id, n32, k, rec[nw], pid[nw], ds);
-        detect_kernel<Real, false><<<gn, 256, 0, st>>>(rec[nw], cell_start, n32, k, entries, entries_cap, head, wl[0], ds, SlabView{});
+        detect_kernel<Real, false><<<(unsigned)((n + DETECT_THREADS - 1) / DETECT_THREADS), DETECT_THREADS, 0, st>>>(rec[nw], cell_start, n32, k, entries, entries_cap, head, wl[0], ds, SlabView{});
         *launches += 7;
         if (capture) {
             count_centre_kernel<Real><<<gn, 256, 0, st>>>(rec[nw], cell_start, n32, k, ctr_count);

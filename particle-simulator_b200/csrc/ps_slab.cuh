@@ -656,8 +656,8 @@ struct SlabCollider {
         if (int d = dbg("move")) return d;
         SlabView sv{g.gl, g.gr, g.ncl, g.col_off, g.gcols, &sd->n_local, &sd->n_blocked, brem};
         const uint64_t n_hi = (uint64_t)n_own_step + 2ull * g.cap_h;             // at most this many local slots after the exchange
-        const unsigned g_det = (unsigned)(((n_hi < g.cap ? n_hi : g.cap) + 255) / 256);
-        detect_kernel<Real, true><<<g_det, 256, 0, st>>>(rec[nw], cell_start, g.cap, k, entries, entries_cap, head, wl[0], ds, sv);
+        const unsigned g_det = (unsigned)(((n_hi < g.cap ? n_hi : g.cap) + DETECT_THREADS - 1) / DETECT_THREADS);
+        detect_kernel<Real, true><<<g_det, DETECT_THREADS, 0, st>>>(rec[nw], cell_start, g.cap, k, entries, entries_cap, head, wl[0], ds, sv);
         launches += 9;
         int rc;
         if (int d = dbg("detect")) return d;
