@@ -261,18 +261,35 @@ __device__ __forceinline__ uint32_t slab_input_pid(uint32_t t, const uint32_t* p
     return j < g.cap_h ? halo_pids<Real>(recv_l, g.cap_h)[j] : halo_pids<Real>(recv_r, g.cap_h)[j - g.cap_h];
 }
 
+// input index space of place / move: [0, n_own_prev) own particles, then the 2 cap_h received records (stored at cap + j)
+__device__ __forceinline__ uint32_t slab_input_index(uint32_t t, uint32_t n_own_prev, const SlabGeom& g) {
+    if (t < n_own_prev) return t;
+    const uint32_t j = t - n_own_prev;
+    return j < 2 * g.cap_h ? g.cap + j : SLAB_INVALID;
+}
+
+// SORT_ILP inputs per thread, CTA-strided, the loads of each step issued together (as place_kernel / move_kernel do)
 template <class Real>
 __global__ void __launch_bounds__(256)
 slab_place_kernel(const uint32_t* __restrict__ slot_cell, const uint32_t* __restrict__ arrival, const uint32_t* __restrict__ pid_old,
                   uint32_t own_b_prev, uint32_t n_own_prev, const uint32_t* __restrict__ cell_start, SlabGeom g, void* recv_l, void* recv_r,
                   uint32_t* __restrict__ tmp_id) {
-    // input index space: [0, n_own_prev) own particles, [cap, cap + 2 cap_h) received records
-    uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= n_own_prev) { t = g.cap + (t - n_own_prev); if (t >= g.cap + 2 * g.cap_h) return; }
-    const uint32_t c = slot_cell[t];
-    if (c == SLAB_INVALID) return;
-    const uint32_t dst = cell_start[c] + arrival[t];
-    if (dst < g.cap) tmp_id[dst] = slab_input_pid<Real>(t, pid_old, own_b_prev, g, recv_l, recv_r);
+    const uint32_t t0 = blockIdx.x * (blockDim.x * SORT_ILP) + threadIdx.x;
+    uint32_t t[SORT_ILP], c[SORT_ILP], a[SORT_ILP], id[SORT_ILP], b[SORT_ILP];
+#pragma unroll
+    for (int j = 0; j < SORT_ILP; ++j) {
+        t[j] = slab_input_index(t0 + j * blockDim.x, n_own_prev, g);
+        c[j] = SLAB_INVALID;
+        if (t[j] != SLAB_INVALID) { c[j] = slot_cell[t[j]]; a[j] = arrival[t[j]]; id[j] = slab_input_pid<Real>(t[j], pid_old, own_b_prev, g, recv_l, recv_r); }
+    }
+#pragma unroll
+    for (int j = 0; j < SORT_ILP; ++j) if (c[j] != SLAB_INVALID) b[j] = cell_start[c[j]];
+#pragma unroll
+    for (int j = 0; j < SORT_ILP; ++j) {
+        if (c[j] == SLAB_INVALID) continue;
+        const uint32_t dst = b[j] + a[j];
+        if (dst < g.cap) tmp_id[dst] = id[j];
+    }
 }
 
 template <class Real>
@@ -281,25 +298,36 @@ slab_move_kernel(const Rec<Real>* __restrict__ rec_old, const uint32_t* __restri
                  const uint32_t* __restrict__ slot_cell, const uint32_t* __restrict__ cell_start, const uint32_t* __restrict__ tmp_id,
                  StepConst<Real> k, SlabGeom g, void* recv_l, void* recv_r, const DevState* __restrict__ ds,
                  Rec<Real>* __restrict__ rec_new, uint32_t* __restrict__ pid_new) {
-    uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= n_own_prev) { t = g.cap + (t - n_own_prev); if (t >= g.cap + 2 * g.cap_h) return; }
-    const uint32_t c = slot_cell[t];
-    if (c == SLAB_INVALID) return;
-    const uint32_t id = slab_input_pid<Real>(t, pid_old, own_b_prev, g, recv_l, recv_r);
-    const uint32_t b = cell_start[c], e = cell_start[c + 1];
-    uint32_t rank = 0;
-    for (uint32_t q = b; q < e && q < g.cap; ++q) rank += tmp_id[q] < id ? 1u : 0u;   // ascending particle index inside the cell (:146-158)
-    Rec<Real> r;
-    if (t < g.cap) {
-        r = ld_rec(rec_old + own_b_prev + t);
-        if (!ds->flags) integrate_rec<Real>(r, k);                           // same arithmetic as slab_bin_kernel, bit for bit
-    } else {
-        const uint32_t j = t - g.cap;
-        r = j < g.cap_h ? ld_rec(halo_recs<Real>(recv_l) + j) : ld_rec(halo_recs<Real>(recv_r) + (j - g.cap_h));
+    const uint32_t t0 = blockIdx.x * (blockDim.x * SORT_ILP) + threadIdx.x;
+    const bool frozen = ds->flags != 0u;
+    uint32_t t[SORT_ILP], c[SORT_ILP], id[SORT_ILP], b[SORT_ILP], e[SORT_ILP];
+    Rec<Real> r[SORT_ILP];
+#pragma unroll
+    for (int j = 0; j < SORT_ILP; ++j) {
+        t[j] = slab_input_index(t0 + j * blockDim.x, n_own_prev, g);
+        c[j] = SLAB_INVALID;
+        if (t[j] == SLAB_INVALID) continue;
+        c[j] = slot_cell[t[j]];
+        id[j] = slab_input_pid<Real>(t[j], pid_old, own_b_prev, g, recv_l, recv_r);
+        if (t[j] < g.cap) {
+            r[j] = ld_rec(rec_old + own_b_prev + t[j]);
+        } else {
+            const uint32_t h = t[j] - g.cap;
+            r[j] = h < g.cap_h ? ld_rec(halo_recs<Real>(recv_l) + h) : ld_rec(halo_recs<Real>(recv_r) + (h - g.cap_h));
+        }
     }
-    if (b + rank >= g.cap) return;                                           // only in an error state (capacity flagged by slab_counts_kernel)
-    st_rec(rec_new + b + rank, r);
-    pid_new[b + rank] = id;
+#pragma unroll
+    for (int j = 0; j < SORT_ILP; ++j) if (c[j] != SLAB_INVALID) { b[j] = cell_start[c[j]]; e[j] = cell_start[c[j] + 1]; }
+#pragma unroll
+    for (int j = 0; j < SORT_ILP; ++j) {
+        if (c[j] == SLAB_INVALID) continue;
+        uint32_t rank = 0;
+        for (uint32_t q = b[j]; q < e[j] && q < g.cap; ++q) rank += tmp_id[q] < id[j] ? 1u : 0u;   // ascending particle index inside the cell (:146-158)
+        if (t[j] < g.cap && !frozen) integrate_rec<Real>(r[j], k);              // same arithmetic as slab_bin_kernel, bit for bit; received records arrive integrated
+        if (b[j] + rank >= g.cap) continue;                                      // only in an error state (capacity flagged by slab_counts_kernel)
+        st_rec(rec_new + b[j] + rank, r[j]);
+        pid_new[b[j] + rank] = id[j];
+    }
 }
 
 // after phase A: do the particles of the last two local columns still have pending pairs?
@@ -640,7 +668,7 @@ struct SlabCollider {
     // stage 2 (recv_l / recv_r hold the neighbours' M0): local sort, detect, phase A, one host synchronisation
     int stage_build() {
         const int nw = cur ^ 1;
-        const unsigned g_cap = (g.cap + 255) / 256, g_in = (n_own_step + 2 * g.cap_h + 255) / 256, g_h = (2 * g.cap_h + 255) / 256;
+        const unsigned g_cap = (g.cap + 255) / 256, g_in = (n_own_step + 2 * g.cap_h + 256 * SORT_ILP - 1) / (256 * SORT_ILP), g_h = (2 * g.cap_h + 255) / 256;
         cudaStream_t st = stream;
         const StepConst<Real>& k = k_step;
         if (int d = dbg("bin")) return d;
