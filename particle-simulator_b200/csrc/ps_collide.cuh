@@ -571,7 +571,7 @@ detect_kernel(const Rec<Real>* __restrict__ rec, const uint32_t* __restrict__ ce
     unsigned long long m64 = 0ull;
     int path = 0;                                            // 0: 32-bit mask, 1: 64-bit mask, 2: generic walk
     OwnFlags own{true, true, true};
-    bool blocked = false;
+    bool blocked = false, first_lower = false;
     if (valid) {
         if (SLAB) {
             // local cell: global computeCoordinate, then shift by the slab's first local column
@@ -600,8 +600,15 @@ detect_kernel(const Rec<Real>* __restrict__ rec, const uint32_t* __restrict__ ce
         path = total + (st.m2 - st.m1) <= 32u ? 0 : (total <= 64u ? 1 : 2);
         if (path == 0) {
             const uint32_t hits = test_flat<Real>(rec, a, pa, st, nL, nM, total, k.r2sq);
-            m32 = list_mask(hits, st, a, nL, nM, list_runs(st, a), own);
+            const ListRuns lr = list_runs(st, a);
+            m32 = list_mask(hits, st, a, nL, nM, lr, own);
             cnt = (uint32_t)__popc(m32);
+            // Round 0 runs a ready pair from its lower slot (resolve_item), so a particle whose first partner has a
+            // lower slot has nothing to do there: it stays off the first work list.  Runs 3, 4, 6, 7 hold the higher slots.
+            if (m32) {
+                const uint32_t p = (uint32_t)__ffs((int)m32) - 1u;
+                first_lower = !((p >= lr.t3 && p < lr.t5) || p >= lr.t6);
+            }
         } else if (path == 1) {
             m64 = test_block<Real, unsigned long long>(rec, a, pa, st, k.r2sq);
             cnt = count_block<unsigned long long, SLAB>(m64, st, nL, nM, own);
@@ -613,7 +620,8 @@ detect_kernel(const Rec<Real>* __restrict__ rec, const uint32_t* __restrict__ ce
         }
     }
     // packed CTA scan: entry count in the low 22 bits, "goes on the first work list" flag above
-    const uint32_t packed = cnt | (((cnt && !blocked) ? 1u : 0u) << 22);
+    const bool listed = cnt && !blocked && !first_lower;
+    const uint32_t packed = cnt | ((listed ? 1u : 0u) << 22);
     uint32_t total;
     const uint32_t ex = block_exclusive_scan<DETECT_THREADS>(packed, &total);
     if (threadIdx.x == 0) {
@@ -646,7 +654,7 @@ detect_kernel(const Rec<Real>* __restrict__ rec, const uint32_t* __restrict__ ce
         });
     }
     if (path != 0) first_entry = entries[begin];
-    if (!blocked) wl0[sh_wbase + (ex >> 22)] = make_uint2(a, first_entry);
+    if (listed) wl0[sh_wbase + (ex >> 22)] = make_uint2(a, first_entry);
 }
 
 
