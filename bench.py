@@ -555,12 +555,24 @@ def run_collide(args):
     launches = st["kernel_launches"]
     sim.close()
     if rank == 0:
+        # whole sub-step against the HBM roofline: algorithmic bytes of its kernels / time per sub-step
+        rec = 16 if args.precision == "f32" else 32                      # one record {x, y, u, w}
+        cells = (int(scene.width) // int(scene.grid_size)) * (int(scene.height) // int(scene.grid_size))
+        pairs = st["pairs_last"] * world                                 # rank 0's last sub-step, all ranks alike
+        per_substep = n * ((rec + 8) + 16 + (2 * rec + 16) + (rec + 12)) + 6 * cells + pairs * (4 * rec + 36)
+        peak, peak_src = hbm_peak()
+        achieved = per_substep / (dt / (K * S)) / 1e9 / world            # per GPU
+        roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                    "kernel": "whole collision sub-step (bin, scans, place, move, detect, resolve)", "peak_source": peak_src,
+                    "algorithmic_bytes_per_substep": per_substep,
+                    "note": "detect and resolve are latency / sector bound, not streaming kernels (DESIGN.md section 4); per GPU"}
         line = {"metric": METRIC, "value": n * S * K / dt, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
                 "ms_per_step": 1e3 * dt / K, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
                 "dtype": args.precision, "data": "synthetic",
                 "config": {"workload": f"{n >> 20}Mi particles, full updatePhysics with uniform-grid collisions (BASELINE.json configs[4]); "
                                        f"step = one frame = 8 sub-steps; x-slab decomposition, NCCL send/recv halo + migration",
                            "particles": n, "sub_steps": S, "timing": "host clock around K frames, sync on both sides, max over ranks"},
+                "roofline": roofline,
                 "gpu_launches": int(launches), "pairs_last_rank0": st["pairs_last"], "rounds_last_rank0": st["rounds_last"],
                 "clocks": clocks.summary()}
         print(json.dumps(line), flush=True)
