@@ -45,6 +45,10 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-extras", action="store_true")
+    ap.add_argument("--no-f64", action="store_true", help="skip the f64 build's roofline / end-to-end figures")
+    ap.add_argument("--no-collide", action="store_true", help="skip the collision scenes (BASELINE.json configs[3], configs[4])")
+    ap.add_argument("--collide-particles", type=int, default=256 << 20, help="particles of the configs[4] collision scene (whole scene, all GPUs)")
+    ap.add_argument("--collide-frames", type=int, default=3, help="timed updatePhysics frames of each collision scene")
     ap.add_argument("--variant", type=int, default=0, help="integrate kernel variant (0 = auto)")
     ap.add_argument("--sweep", action="store_true", help="time every integrate kernel variant and print a table to stderr")
     ap.add_argument("--ref-sample", type=int, default=4 << 20, help="particles per step of the CPU reference arm")
@@ -170,7 +174,9 @@ def run_reference(args):
 def workload_config(args, precision):
     return {
         "workload": f"{args.particles >> 20}Mi particles per GPU, integrate + wall bounce "
-                    f"(BASELINE.json configs[2]); step = one updatePhysics frame = 8 sub-steps",
+                    f"(BASELINE.json configs[2]); step = one updatePhysics frame = 8 sub-steps; value / roofline: {precision} arithmetic "
+                    f"on {precision} SoA state (roofline.f64: the f64 build); e2e: f64 host arrays, f64 arithmetic (core.zig as written), "
+                    f"e2e.f32_host_f32_device: f32 both sides; collision scenes: see config.collide_* and the trailing `collide` object",
         "particles_per_gpu": args.particles, "sub_steps": 8, "scene": "reference constants, world at 0.444 particles/cell",
         "sharding": "particle index range per rank, no collective",
         "l2": f"state >= {args.particles * 16 >> 20} MiB per GPU (fp32 SoA), larger than the 126 MB L2: no flush needed",
@@ -350,27 +356,88 @@ def run_ours(args):
     achieved = n * BYTES_PER_UPDATE[prec] / (launch_ms * 1e-3) / 1e9
     peak, peak_src = hbm_peak()
 
-    # ---- end to end through the C ABI from host buffers
-    e2e = None
-    if not args.no_e2e:
-        def frame():
-            # Solver.updatePhysics on host slices: H2D of this frame's inputs (positions + velocities, pinned host memory
-            # in core.zig's f64 layout), the 8 sub-steps, D2H of the result (positions: what main.zig reads to draw)
-            sim.frame_host(hp, hv, ho, None, 1)
+    # ---- the f64 build of the same kernel (core.zig as written, src/core.zig:5): its own roofline figures
+    roof64 = None
+    if prec == "f32" and not args.no_f64:
+        with Simulation(scene, precision="f64", collisions=False, device=local) as s64:
+            s64.set_stream(stream)
+            s64.upload(hp, hv)
+            timed(torch, dist, lambda: s64.step(1), W)
+            k64 = max(3, min(K, 20))
+            ms64 = timed(torch, dist, lambda: s64.step(1), k64)
+            lm64 = ms64 / (k64 * S)
+            a64 = n * BYTES_PER_UPDATE["f64"] / (lm64 * 1e-3) / 1e9
+            roof64 = {"achieved": a64, "frac": a64 / peak, "launch_ms": lm64, "value": n_total * S * k64 / (ms64 * 1e-3), "unit": UNIT,
+                      "kernel": "integrate_bounce_kernel<double>", "algorithmic_bytes_per_launch": n * BYTES_PER_UPDATE["f64"]}
 
+            # ---- end to end through the C ABI from host buffers, like for like with core.zig: f64 host arrays
+            # ([]@Vector(2,f64)), f64 arithmetic on the device, f64 results — bit-identical to the reference's step
+            e2e = None
+            if not args.no_e2e:
+                def frame64():
+                    # Solver.updatePhysics on host slices: H2D of this frame's inputs (positions + velocities, pinned host
+                    # memory), the 8 sub-steps, D2H of the result (positions: what main.zig reads to draw)
+                    s64.frame_host(hp, hv, ho, None, 1)
+
+                ke = max(3, min(K, 10))
+                timed(torch, dist, frame64, 2)
+                ms_e = timed(torch, dist, frame64, ke)
+                e2e = {"value": n_total * S * ke / (ms_e * 1e-3), "unit": UNIT,
+                       "h2d_bytes_per_step": int(hp.nbytes + hv.nbytes), "d2h_bytes_per_step": int(ho.nbytes),
+                       "ms_per_step": ms_e / ke, "steps": ke, "host_dtype": "f64", "device_dtype": "f64",
+                       "api": "ps_frame_host(f64 pos_in, vel_in -> pos_out) on an f64 handle, pinned host buffers, "
+                              "2 Mi-particle chunks over 4 streams, copy engines both ways",
+                       "f64_device": {"value": n_total * S * ke / (ms_e * 1e-3), "ms_per_step": ms_e / ke}}
+    else:
+        e2e = None
+    # the fp32 pair: f32 host arrays, f32 arithmetic (north_star's layout; half the bytes over the host link)
+    if not args.no_e2e:
+        h32 = [torch.empty((n, 2), dtype=torch.float32, pin_memory=True) for _ in range(3)]
+        a32 = [t.numpy() for t in h32]
+        a32[0][...] = hp
+        a32[1][...] = hv
         ke = max(3, min(K, 10))
-        timed(torch, dist, frame, 2)
-        ms_e = timed(torch, dist, frame, ke)
-        e2e = {"value": n_total * S * ke / (ms_e * 1e-3), "unit": UNIT,
-               "h2d_bytes_per_step": int(hp.nbytes + hv.nbytes), "d2h_bytes_per_step": int(ho.nbytes),
-               "ms_per_step": ms_e / ke, "steps": ke,
-               "api": "ps_frame_host(f64 pos_in, vel_in -> pos_out), pinned host buffers, 2 Mi-particle chunks over 4 streams, copy engines both ways"}
+        timed(torch, dist, lambda: sim.frame_host(a32[0], a32[1], a32[2], None, 1), 2)
+        ms32 = timed(torch, dist, lambda: sim.frame_host(a32[0], a32[1], a32[2], None, 1), ke)
+        f32_pair = {"value": n_total * S * ke / (ms32 * 1e-3), "ms_per_step": ms32 / ke, "host_dtype": "f32", "device_dtype": "f32",
+                    "h2d_bytes_per_step": int(a32[0].nbytes + a32[1].nbytes), "d2h_bytes_per_step": int(a32[2].nbytes),
+                    "api": "ps_frame_host_f32 on the f32 handle"}
+        # what main.zig's draw loop actually needs each frame (src/main.zig:102-107): the state stays on the GPU, the
+        # step runs there, and only positions come back, as f32 (the f64 -> f32 cast of :104-105 done on the device)
+        pos32 = a32[2]
+        def resident_frame():
+            sim.step(1)
+            sim.download(pos32, None)
+        timed(torch, dist, resident_frame, 2)
+        ms_r = timed(torch, dist, resident_frame, ke)
+        resident = {"value": n_total * S * ke / (ms_r * 1e-3), "ms_per_step": ms_r / ke, "h2d_bytes_per_step": 0,
+                    "d2h_bytes_per_step": int(pos32.nbytes),
+                    "note": "state resident on the GPU, one updatePhysics frame, positions read back as f32 (what main.zig draws from)"}
+        del h32, a32, pos32
+        if e2e is None:      # --precision f64 or --no-f64: the pair that matches the handle's own type
+            e2e = {"value": f32_pair["value"], "unit": UNIT, "h2d_bytes_per_step": f32_pair["h2d_bytes_per_step"],
+                   "d2h_bytes_per_step": f32_pair["d2h_bytes_per_step"], "ms_per_step": f32_pair["ms_per_step"], "steps": ke,
+                   "host_dtype": "f32", "device_dtype": prec, "api": f32_pair["api"]}
+        e2e["f32_host_f32_device"] = f32_pair
+        e2e["resident_pos_f32"] = resident
+        # the host link is the ceiling (tools/pcie_probe.py; profiles/): ~55 GB/s each way for one process, and the
+        # processes of one box share the host's memory system, so the aggregate does not grow with N
+        e2e["bound"] = "host link (PCIe 5 x16 per GPU; all ranks share one host memory system)"
+        gbs = (e2e["h2d_bytes_per_step"] + e2e["d2h_bytes_per_step"]) / (e2e["ms_per_step"] * 1e-3) / 1e9
+        e2e["link_gbs_per_rank"] = gbs
+        e2e["link_gbs_aggregate"] = gbs * world
     clocks.stop()
 
     extras = {}
     if not args.no_extras and rank == 0 and world == 1:
         extras = run_extras(torch, sim, scene, hp, hv, n, S, prec)
     sim.close()
+    del host_pos, host_vel, host_out, hp, hv, ho
+
+    # ---- the collision-bearing configurations (BASELINE.json configs[3] and configs[4]); every rank takes part
+    collide = None
+    if not args.no_collide:
+        collide = collide_block(torch, dist, args, rank, world, local)
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -393,14 +460,23 @@ def run_ours(args):
         dist.barrier()
     if rank == 0:
         kernel = f"integrate_bounce_kernel<{'float' if prec == 'f32' else 'double'}>"
+        config = workload_config(args, prec)
+        if collide:
+            # the headline numbers of the collision scenes again, where the driver keeps the whole object
+            for key in ("collide_256Mi", "collide_16Mi"):
+                if key in collide and "error" not in collide[key]:
+                    c = collide[key]
+                    config[key] = {k: c.get(k) for k in ("updates_per_s", "ms_per_substep", "pairs", "rounds", "n_gpus", "scaling",
+                                                          "roofline_frac", "slab_parity", "nccl_ranks") if k in c}
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": prec, "data": "synthetic",
-            "config": workload_config(args, prec),
+            "config": config,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": ncu_traffic(kernel), "kernel": kernel, "peak_source": peak_src,
-                         "algorithmic_bytes_per_launch": n * BYTES_PER_UPDATE[prec], "launch_ms": launch_ms},
+                         "traffic": ncu_traffic(kernel), "traffic_source": "committed ncu --set full capture (profiles/roofline_traffic.json), not this run",
+                         "kernel": kernel, "peak_source": peak_src,
+                         "algorithmic_bytes_per_launch": n * BYTES_PER_UPDATE[prec], "launch_ms": launch_ms, "f64": roof64},
             "cpu_baseline": cpu,
             "e2e": e2e,
             "gpu_launches": int(launches),
@@ -408,10 +484,231 @@ def run_ours(args):
         }
         if extras:
             line["extra"] = extras
+        if collide:
+            line["collide"] = collide      # last key: the driver's stdout tail keeps the end of the line
         print(json.dumps(line), flush=True)
     if dist is not None:
         dist.destroy_process_group()
     return 0
+
+
+# ------------------------------------------------------------------------------------------------
+# collision scenes inside the default run
+# ------------------------------------------------------------------------------------------------
+def substep_algorithmic_bytes(n, cells, pairs, precision):
+    """Algorithmic bytes of one collision sub-step: the sum over its kernels."""
+    rec = 16 if precision == "f32" else 32                      # one record {x, y, u, w}
+    return n * ((rec + 8) + 16 + (2 * rec + 16) + (rec + 12)) + 6 * cells + pairs * (4 * rec + 36)
+
+
+def scene_cells(scene):
+    return (int(scene.width) // int(scene.grid_size)) * (int(scene.height) // int(scene.grid_size))
+
+
+def time_collision_scene(torch, dist, sim, scene, frames, warm_frames, world, precision, local):
+    """Warm up, then time `frames` updatePhysics frames of a collision handle (single-GPU or slab) with CUDA events
+    on the launching stream, barrier + synchronize on both sides, max over ranks.  Returns the result block."""
+    S = scene.sub_steps
+    stream = torch.cuda.current_stream().cuda_stream
+    sim.set_stream(stream)
+    for _ in range(max(warm_frames, 1)):
+        sim.step(1)
+    sim.sync()
+    clocks = ClockSampler(local)
+    clocks.start()
+    l0 = sim.stats()["kernel_launches"]
+
+    def frame():
+        sim.step(1)
+
+    ms = timed(torch, dist, frame, frames)
+    sim.sync()                                                   # surfaces any error flag raised by the last sub-step
+    clocks.stop()
+    st = sim.stats()
+    pairs, rounds = st["pairs_last"], st["rounds_last"]
+    if dist is not None:
+        t = torch.tensor([pairs], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        pairs = int(t.item())
+        t = torch.tensor([rounds], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        rounds = int(t.item())
+    n = scene.count
+    ms_sub = ms / (frames * S)
+    per_substep = substep_algorithmic_bytes(n, scene_cells(scene), pairs, precision)
+    peak, peak_src = hbm_peak()
+    achieved = per_substep / (ms_sub * 1e-3) / 1e9 / world      # per GPU
+    return {"updates_per_s": n * S * frames / (ms * 1e-3), "ms_per_substep": ms_sub, "ms_per_frame": ms / frames,
+            "pairs": pairs, "rounds": rounds, "n_gpus": world, "particles": n, "frames": frames, "warm_frames": warm_frames,
+            "dtype": precision, "gpu_launches": int(st["kernel_launches"] - l0),
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                         "kernel": "whole collision sub-step (bin, scans, place, move, detect, resolve)", "peak_source": peak_src,
+                         "algorithmic_bytes_per_substep": per_substep,
+                         "note": "per GPU; detect and resolve are latency / sector bound, not streaming kernels (DESIGN.md section 4)"},
+            "roofline_frac": achieved / peak, "clocks": clocks.summary(),
+            "timing": "CUDA events on the launching stream around the frames, barrier + synchronize on both sides, max over ranks"}
+
+
+def collide_block(torch, dist, args, rank, world, local):
+    """BASELINE.json configs[4] (one 256 Mi-particle collision scene on all N GPUs: the single-GPU handle at N = 1,
+    x-slabs with NCCL send/recv of migrants, halo and boundary states at N > 1; strong scaling) and, at N = 1,
+    configs[3] (16 Mi particles).  At N > 1 a 1 Mi-particle scene also runs 24 sub-steps through the same NCCL path
+    and is compared with the CPU oracle bit for bit: the run fails if it differs."""
+    from particle_simulator_b200 import Simulation, SlabSimulation, scenes
+
+    prec = "f32"
+    out = {"precision": prec, "scaling": "strong"}
+    frames = max(1, args.collide_frames)
+    gloo = dist.new_group(backend="gloo") if world > 1 else None     # host-side object gathers (results, stage times)
+
+    def new_slab(scene, contacts=0):
+        idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            idt = torch.frombuffer(bytearray(SlabSimulation.unique_id()), dtype=torch.uint8).clone().cuda()
+        dist.broadcast(idt, 0)
+        return SlabSimulation(scene, rank, world, bytes(idt.cpu().numpy().tobytes()), precision=prec, device=local,
+                              contacts_per_particle=contacts)
+
+    # ---- configs[4]
+    n_big = args.collide_particles
+    scene = scenes.scaled_scene(n_big)
+    key = "collide_256Mi" if n_big == 256 << 20 else f"collide_{n_big >> 20}Mi"
+    try:
+        sim = new_slab(scene) if world > 1 else Simulation(scene, precision=prec, collisions=True, device=local)
+        try:
+            sim.spawn(1)
+            blk = time_collision_scene(torch, dist, sim, scene, frames, 2, world, prec, local)
+            blk["scaling"] = "strong"
+            blk["workload"] = (f"{n_big >> 20}Mi particles, one scene on {world} GPU(s), full updatePhysics with uniform-grid collisions "
+                               f"(BASELINE.json configs[4]), fp32; " +
+                               ("x-slabs of whole cell columns, NCCL send/recv of migrants + halo + boundary states" if world > 1
+                                else "single-GPU handle (ps_step)"))
+            if world > 1:
+                blk["nccl_ranks"] = world
+                blk["path"] = "ps_slab_* (csrc/ps_slab.cuh) over ncclSend/ncclRecv"
+                # per-stage breakdown: a second, shorter run with the stage events switched on (one more synchronisation per
+                # sub-step, so it is not the run that is timed above)
+                sim.set_timing(True)
+                sim.step(3)
+                sim.sync()
+                tm = sim.timing()
+                sim.set_timing(False)
+                parts = [None] * world
+                dist.all_gather_object(parts, tm, group=gloo)
+                blk["stage_us_per_substep"] = {"rank0": parts[0], "max_over_ranks": {k: max(p[k] for p in parts) for k in parts[0]},
+                                               "note": "PS_SLAB_TIMING stages, CUDA events, 16 sub-steps after 8 discarded"}
+            out[key] = blk
+        finally:
+            sim.close()
+    except Exception as e:  # noqa: BLE001
+        out[key] = {"error": f"{type(e).__name__}: {e}"}
+        log(f"[rank {rank}] collision scene failed: {e}")
+
+    # ---- N > 1: the NCCL path against the oracle, bit for bit
+    if world > 1:
+        out["slab_parity"] = slab_parity(torch, dist, gloo, rank, world, local, new_slab, prec)
+        if key in out and "error" not in out[key]:
+            out[key]["slab_parity"] = out["slab_parity"]["result"]
+        if out["slab_parity"]["result"] != "bit-exact":
+            raise SystemExit(f"bench.py: slab path differs from the oracle: {out['slab_parity']}")
+
+    # ---- configs[0] after pressing `g` (src/main.zig:124): the shipped 13 000-particle scene settled into a pile under
+    # gravity, the deep-dependency-chain case of the exact-order resolve; frames 100-125, f64, against the CPU port
+    if world == 1:
+        try:
+            out["gravity_pile_13k"] = gravity_pile(torch, local)
+        except Exception as e:  # noqa: BLE001
+            out["gravity_pile_13k"] = {"error": f"{type(e).__name__}: {e}"}
+
+    # ---- configs[3] (one GPU)
+    if world == 1:
+        try:
+            cs = scenes.scaled_scene(16 << 20)
+            with Simulation(cs, precision=prec, collisions=True, device=local) as c:
+                c.spawn(1)
+                blk = time_collision_scene(torch, None, c, cs, frames, 2, 1, prec, local)
+                blk["workload"] = "16Mi particles, full updatePhysics with uniform-grid collisions (BASELINE.json configs[3]), fp32, one GPU"
+                out["collide_16Mi"] = blk
+        except Exception as e:  # noqa: BLE001
+            out["collide_16Mi"] = {"error": f"{type(e).__name__}: {e}"}
+    return out
+
+
+def gravity_pile(torch, local, settle_frames=100, timed_frames=25):
+    """The default main.zig scene with gravity on (key `g`): settle, then time frames 100-125 on the GPU (f64, one
+    handle, device-resident) and on the CPU port (single thread) from the same state; final states compared bit for bit."""
+    import oracle   # checker + CPU baseline of this case only
+    from particle_simulator_b200 import Simulation, scenes
+
+    sc = scenes.default_scene()
+    S = sc.sub_steps
+    pos0, vel0 = scenes.spawn(sc, seed=1, dtype=np.float64)
+    p, v = pos0.copy(), vel0.copy()
+    params = oracle.make_params()
+    oracle.run(params, p, v, settle_frames * S, collisions=True, t_acc=True)
+    cpu = oracle.run(params, p, v, timed_frames * S, collisions=True, t_acc=True)
+    with Simulation(sc, precision="f64", collisions=True, device=local) as c:
+        c.set_stream(torch.cuda.current_stream().cuda_stream)
+        c.upload(pos0, vel0)
+        c.set_acc(True)
+        c.step(settle_frames)
+        c.sync()
+        r0 = c.stats()["rounds_total"]
+        ms = timed(torch, None, lambda: c.step(timed_frames), 1)
+        st = c.stats()
+        gp, gv = c.download(dtype=np.float64)
+    n_up = sc.count * S * timed_frames
+    same = bool(np.array_equal(gp.view(np.uint8), p.view(np.uint8)) and np.array_equal(gv.view(np.uint8), v.view(np.uint8)))
+    return {"gpu_updates_per_s": n_up / (ms * 1e-3), "gpu_ms_per_substep": ms / (S * timed_frames),
+            "cpu_port_updates_per_s": n_up / cpu["seconds"], "cpu_ms_per_substep": 1e3 * cpu["seconds"] / (S * timed_frames),
+            "speedup_vs_cpu_port": (cpu["seconds"] * 1e3) / ms, "bit_identical": same,
+            "rounds_per_substep": (st["rounds_total"] - r0) / (S * timed_frames), "pairs_last": st["pairs_last"], "dtype": "f64",
+            "workload": f"default scene (13 000 particles, 720x640) with gravity on, frames {settle_frames}-{settle_frames + timed_frames} "
+                        f"(settled pile), full updatePhysics; CPU = oracle/core_ref.hpp, one thread"}
+
+
+def slab_parity(torch, dist, g, rank, world, local, new_slab, prec, n=1 << 20, substeps=24):
+    """1 Mi particles, 24 sub-steps through ps_slab_* over NCCL on all ranks, gathered on rank 0 and compared with the
+    CPU oracle (the checker, outside every timed region): positions, velocities and the pair total, bit for bit."""
+    from particle_simulator_b200 import scenes
+
+    scene = scenes.scaled_scene(n)
+    sim = new_slab(scene, contacts=24)
+    try:
+        sim.spawn(1)
+        sim.step_substeps(substeps)
+        sim.sync()
+        ids, p, v = sim.download_owned()
+        st = sim.stats()
+    finally:
+        sim.close()
+    parts = [None] * world
+    dist.all_gather_object(parts, (ids, p, v, st["pairs_total"]), group=g)
+    res = [None]
+    if rank == 0:
+        import oracle   # checker only
+
+        dtype = np.float32 if prec == "f32" else np.float64
+        pos0, vel0 = scenes.spawn(scene, seed=1)
+        wp, wv = pos0.astype(dtype), vel0.astype(dtype)
+        params = oracle.make_params(radius=scene.radius, width=scene.width, height=scene.height, grid_size=scene.grid_size)
+        o = oracle.run(params, wp, wv, substeps, collisions=True)
+        gp = np.full((n, 2), np.nan)
+        gv = np.full((n, 2), np.nan)
+        seen = np.zeros(n, dtype=np.int64)
+        for i_, p_, v_, _ in parts:
+            ii = i_.astype(np.int64)
+            gp[ii] = p_
+            gv[ii] = v_
+            np.add.at(seen, ii, 1)
+        pairs = int(sum(x[3] for x in parts))
+        ok = bool((seen == 1).all() and np.array_equal(gp.astype(dtype).view(np.uint8), wp.view(np.uint8)) and
+                  np.array_equal(gv.astype(dtype).view(np.uint8), wv.view(np.uint8)) and pairs == o["stats"]["pairs_total"])
+        res[0] = {"result": "bit-exact" if ok else "MISMATCH", "particles": n, "substeps": substeps, "ranks": world, "dtype": prec,
+                  "pairs_total": pairs, "oracle_pairs_total": o["stats"]["pairs_total"],
+                  "checked": "every particle owned once; positions, velocities bit-identical to oracle/core_ref.hpp; pair totals equal"}
+    dist.broadcast_object_list(res, 0, group=g)
+    return res[0]
 
 
 def run_extras(torch, sim, scene, hp, hv, n, S, prec):
@@ -431,48 +728,6 @@ def run_extras(torch, sim, scene, hp, hv, n, S, prec):
                                   "note": f"{S} sub-steps per pass in registers (bit-identical); bytes/update = {BYTES_PER_UPDATE[prec]}/{S}"}
     except Exception as e:
         out["fused_frame"] = {"error": str(e)}
-    other = "f64" if prec == "f32" else "f32"
-    try:
-        with Simulation(scene, precision=other, collisions=False) as s2:
-            s2.set_stream(stream)
-            s2.upload(hp, hv)
-            timed(torch, None, lambda: s2.step(1), 3)
-            ms = timed(torch, None, lambda: s2.step(1), 20)
-            gbs = n * BYTES_PER_UPDATE[other] * S * 20 / (ms * 1e-3) / 1e9
-            out[f"integrate_{other}"] = {"value": n * S * 20 / (ms * 1e-3), "unit": UNIT, "hbm_gbs": gbs}
-    except Exception as e:
-        out[f"integrate_{other}"] = {"error": str(e)}
-    # the same end-to-end frame with f32 host buffers (ps_frame_host_f32): half the bytes over the host link
-    try:
-        h32 = [torch.empty((n, 2), dtype=torch.float32, pin_memory=True) for _ in range(3)]
-        a32 = [t.numpy() for t in h32]
-        a32[0][...] = hp
-        a32[1][...] = hv
-        timed(torch, None, lambda: sim.frame_host(a32[0], a32[1], a32[2], None, 1), 2)
-        ms = timed(torch, None, lambda: sim.frame_host(a32[0], a32[1], a32[2], None, 1), 5)
-        out["e2e_f32_host"] = {"value": n * S * 5 / (ms * 1e-3), "unit": UNIT, "ms_per_step": ms / 5,
-                               "h2d_bytes_per_step": int(a32[0].nbytes + a32[1].nbytes), "d2h_bytes_per_step": int(a32[2].nbytes),
-                               "note": "ps_frame_host_f32: a host that keeps f32 arrays; the headline e2e uses core.zig's f64 layout"}
-        del h32, a32
-    except Exception as e:
-        out["e2e_f32_host"] = {"error": str(e)}
-    try:
-        nc = 16 << 20
-        cs = scenes.scaled_scene(nc)
-        pos = np.empty((nc, 2), dtype=np.float32)
-        vel = np.empty((nc, 2), dtype=np.float32)
-        spawn_chunked(cs, 1, 0, nc, np.float32, pos, vel)
-        with Simulation(cs, precision="f32", collisions=True) as c:
-            c.set_stream(stream)
-            c.upload(pos, vel)
-            timed(torch, None, lambda: c.step(1), 2)
-            ms = timed(torch, None, lambda: c.step(1), 3)
-            st = c.stats()
-            out["collide_16Mi_f32"] = {"value": nc * S * 3 / (ms * 1e-3), "unit": UNIT, "ms_per_substep": ms / (3 * S),
-                                       "pairs_last": st["pairs_last"], "rounds_last": st["rounds_last"],
-                                       "note": "BASELINE.json configs[3]: full updatePhysics with exact-order resolve"}
-    except Exception as e:
-        out["collide_16Mi_f32"] = {"error": str(e)}
     # BASELINE.md section 3, runs B1-B4: the CPU port (f64 unless noted, one thread) beside the same scene on the GPU
     try:
         import oracle

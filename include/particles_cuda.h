@@ -237,6 +237,14 @@ int ps_slab_owned_count(ps_slab* slab, uint64_t* count);
 int ps_slab_download_owned(ps_slab* slab, uint64_t* ids, double* pos_xy, double* vel_xy, uint64_t cap, uint64_t* count);
 int ps_slab_get_stats(ps_slab* slab, ps_stats* out);           /* pairs_* count the pairs whose centre this rank owns */
 const char* ps_slab_last_error(const ps_slab* slab);
+/* Where a sub-step's time goes on this rank (no counterpart in the reference; the measurement SURVEY 8d/8e asks for).
+ * ps_slab_set_timing(slab, 1) brackets the stages of every following sub-step with CUDA events (one extra stream
+ * synchronisation per sub-step, so switch it off for throughput runs); the first 8 sub-steps after switching on are
+ * discarded.  ps_slab_get_timing returns microseconds per sub-step for the stages, in order: bin (integrate + count),
+ * M0 exchange, sort + detect, resolve phase A + boundary check, read-back, M1 exchange, phase B, finish. */
+#define PS_SLAB_TIMING_STAGES 8
+int ps_slab_set_timing(ps_slab* slab, int on);
+int ps_slab_get_timing(ps_slab* slab, double* stage_us, uint32_t cap, uint64_t* substeps);
 
 /* The same slab decomposition with all ranks emulated in ONE process on ONE GPU (device copies where the
  * multi-process path has NCCL messages).  Same kernels, same protocol, same results; it exists so that the

@@ -118,6 +118,8 @@ SYMBOLS = {
     "ps_slab_set_acc": (ctypes.c_int, [_P, ctypes.c_int]),
     "ps_slab_sync": (ctypes.c_int, [_P]),
     "ps_slab_set_stream": (ctypes.c_int, [_P, _P]),
+    "ps_slab_set_timing": (ctypes.c_int, [_P, ctypes.c_int]),
+    "ps_slab_get_timing": (ctypes.c_int, [_P, _PD, ctypes.c_uint32, _PU64]),
     "ps_slab_columns": (ctypes.c_int, [_P, _PU64, _PU64]),
     "ps_slab_owned_count": (ctypes.c_int, [_P, _PU64]),
     "ps_slab_download_owned": (ctypes.c_int, [_P, _P, _P, _P, _U64, _PU64]),

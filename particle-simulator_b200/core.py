@@ -446,6 +446,20 @@ class SlabSimulation:
     def set_stream(self, cuda_stream: int | None) -> None:
         self._check(self._L.ps_slab_set_stream(self._h, ctypes.c_void_p(cuda_stream or 0)))
 
+    TIMING_STAGES = ("bin", "M0", "sort+detect", "resolve A+check", "read-back", "M1", "phase B", "finish")
+
+    def set_timing(self, on: bool) -> None:
+        self._check(self._L.ps_slab_set_timing(self._h, int(on)))
+
+    def timing(self) -> dict:
+        """Microseconds per sub-step of every stage on this rank since set_timing(True) (first 8 sub-steps discarded)."""
+        us = (ctypes.c_double * len(self.TIMING_STAGES))()
+        n = ctypes.c_uint64()
+        self._check(self._L.ps_slab_get_timing(self._h, us, len(self.TIMING_STAGES), ctypes.byref(n)))
+        out = {k: float(us[i]) for i, k in enumerate(self.TIMING_STAGES)}
+        out["substeps"] = int(n.value)
+        return out
+
     def columns(self):
         a, b = ctypes.c_uint64(), ctypes.c_uint64()
         self._check(self._L.ps_slab_columns(self._h, ctypes.byref(a), ctypes.byref(b)))

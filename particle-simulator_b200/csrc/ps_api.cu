@@ -659,6 +659,8 @@ struct ps_slab {
     virtual int stats(ps_stats* out) = 0;
     virtual const char* last_error() const = 0;
     virtual uint64_t sub_steps() const = 0;
+    virtual int set_timing(bool on) = 0;
+    virtual int get_timing(double* us, uint32_t cap, uint64_t* substeps) = 0;
 };
 
 namespace {
@@ -690,6 +692,15 @@ struct SlabT final : ps_slab {
     int stats(ps_stats* out) override { DeviceGuard g(c.device); return c.stats(out); }
     const char* last_error() const override { return c.err.text.c_str(); }
     uint64_t sub_steps() const override { return c.cfg.sub_steps; }
+    int set_timing(bool on) override { DeviceGuard g(c.device); c.set_timing(on); return PS_OK; }
+    int get_timing(double* us, uint32_t cap, uint64_t* substeps) override {
+        DeviceGuard g(c.device);
+        cudaStreamSynchronize(c.stream);
+        const uint64_t nsub = c.timed_substeps();
+        if (substeps) *substeps = nsub;
+        for (uint32_t i = 0; i < cap; ++i) us[i] = (i + 1 < (uint32_t)c.kTicks && nsub) ? c.acc_ms[i + 1] * 1e3 / (double)nsub : 0.0;
+        return PS_OK;
+    }
 };
 
 template <class Real>
@@ -747,6 +758,10 @@ int ps_slab_download_owned(ps_slab* s, uint64_t* ids, double* pos, double* vel, 
 }
 int ps_slab_get_stats(ps_slab* s, ps_stats* out) { return (s && out) ? s->stats(out) : PS_ERR_BAD_ARG; }
 const char* ps_slab_last_error(const ps_slab* s) { return s ? s->last_error() : g_create_error.c_str(); }
+int ps_slab_set_timing(ps_slab* s, int on) { return s ? s->set_timing(on != 0) : PS_ERR_BAD_ARG; }
+int ps_slab_get_timing(ps_slab* s, double* stage_us, uint32_t cap, uint64_t* substeps) {
+    return (s && (stage_us || !cap)) ? s->get_timing(stage_us, cap, substeps) : PS_ERR_BAD_ARG;
+}
 
 // ---- several slab ranks emulated in one process ---------------------------------------------------------------
 }  // extern "C"

@@ -439,7 +439,7 @@ struct SlabCollider {
     cudaEvent_t ev[kTicks] = {};
     bool ev_set[kTicks] = {};
     double acc_ms[kTicks] = {};
-    double host_wait_ms = 0;
+    uint64_t timing_from = 0;      // sub-steps done when timing was switched on
     void tick(int i) {
         if (!timing) return;
         if (!ev[i]) cudaEventCreate(&ev[i]);
@@ -449,7 +449,7 @@ struct SlabCollider {
     void tock() {
         if (!timing) return;
         cudaStreamSynchronize(stream);
-        if (substeps_done <= kTimingSkip) { for (int i = 0; i < kTicks; ++i) { acc_ms[i] = 0; ev_set[i] = false; } return; }   // connection set-up, first sort
+        if (substeps_done <= timing_from + kTimingSkip) { for (int i = 0; i < kTicks; ++i) { acc_ms[i] = 0; ev_set[i] = false; } return; }   // connection set-up, first sort
         int prev = -1;
         for (int i = 0; i < kTicks; ++i) {
             if (!ev_set[i]) continue;
@@ -457,9 +457,17 @@ struct SlabCollider {
             prev = i; ev_set[i] = false;
         }
     }
+    // ps_slab_set_timing / ps_slab_get_timing: the same figures through the C ABI (stages 1..8, microseconds per sub-step)
+    void set_timing(bool on) {
+        cudaStreamSynchronize(stream);
+        timing = on;
+        timing_from = substeps_done;
+        for (int i = 0; i < kTicks; ++i) { acc_ms[i] = 0; ev_set[i] = false; }
+    }
+    uint64_t timed_substeps() const { return substeps_done > timing_from + kTimingSkip ? substeps_done - timing_from - kTimingSkip : 0; }
     void report() {
-        if (!timing || substeps_done <= kTimingSkip) return;
-        const double nsub = (double)(substeps_done - kTimingSkip);
+        if (!timing || timed_substeps() == 0) return;
+        const double nsub = (double)timed_substeps();
         static const char* names[kTicks] = {"", "bin", "M0", "sort+detect", "resolve A+check", "readback", "M1", "phase B", "finish"};
         std::string line = "[slab timing] rank " + std::to_string(rank) + " per sub-step (us):";
         for (int i = 1; i < kTicks; ++i) line += std::string(" ") + names[i] + "=" + std::to_string((int)(acc_ms[i] * 1e3 / nsub));
