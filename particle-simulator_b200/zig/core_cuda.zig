@@ -17,7 +17,7 @@ pub const c = @cImport({
     @cInclude("particles_cuda.h");
 });
 
-pub const BackendError = error{ BadArgument, OutOfMemory, CudaFailure, NcclFailure, CellOverflow, ContactCapacity, NoDevice };
+pub const BackendError = error{ BadArgument, OutOfMemory, CudaFailure, NcclFailure, CellOverflow, ContactCapacity, NoDevice, Migration };
 
 fn check(rc: c_int) BackendError!void {
     return switch (rc) {
@@ -28,6 +28,7 @@ fn check(rc: c_int) BackendError!void {
         c.PS_ERR_CELL_OVERFLOW => BackendError.CellOverflow,
         c.PS_ERR_CAPACITY => BackendError.ContactCapacity,
         c.PS_ERR_NO_DEVICE => BackendError.NoDevice,
+        c.PS_ERR_MIGRATION => BackendError.Migration,
         else => BackendError.CudaFailure,
     };
 }

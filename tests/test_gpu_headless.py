@@ -36,7 +36,7 @@ def replay(frames, keys, scene, pos, vel):
     return pos, vel, stepped
 
 
-@pytest.mark.parametrize("precision", ["f64"])
+@pytest.mark.parametrize("precision", ["f64", "f32"])
 def test_headless_driver_replays_main_zig(tmp_path, precision):
     exe = build.build_headless()
     assert exe and os.path.exists(exe)
@@ -53,7 +53,10 @@ def test_headless_driver_replays_main_zig(tmp_path, precision):
     vel = raw[8 + n * 16:8 + 2 * n * 16].view(np.float64).reshape(n, 2)
     scene = scenes.default_scene()
     pos0, vel0 = scenes.spawn(scene, seed=3)          # the C++ Spawner uses the same counter-based generator
-    want_p, want_v, stepped = replay(40, keys, scene, pos0, vel0)
+    dt = np.float64 if precision == "f64" else np.float32
+    # an f32 handle rounds the caller's f64 arrays once at upload and hands back widened f32 values: the oracle
+    # runs in the same type from the same rounded start
+    want_p, want_v, stepped = replay(40, keys, scene, pos0.astype(dt), vel0.astype(dt))
     assert info["frames"] == stepped and info["substeps"] == stepped * 8
-    assert_bit_exact(pos.copy(), want_p, "positions")
-    assert_bit_exact(vel.copy(), want_v, "velocities")
+    assert_bit_exact(pos.copy(), want_p.astype(np.float64), "positions")
+    assert_bit_exact(vel.copy(), want_v.astype(np.float64), "velocities")

@@ -1,9 +1,11 @@
 """GPU parity of the after-step kernels: rainbow colours, draw rectangles, headless frame.
-Checked against numpy restatements of src/main.zig:102-107, src/gui.zig:83-86, src/core.zig:411-417 and src/colors.zig."""
+Checked against numpy restatements of src/main.zig:102-107, src/gui.zig:83-86 written here, and the oracle's restatement of
+src/core.zig:411-417 + src/colors.zig (oracle/colors_ref.py, pinned by the hand KATs of tests/test_oracle_colors.py)."""
 import numpy as np
 import pytest
 
-from particle_simulator_b200 import Simulation, core, scenes
+from oracle import colors_ref
+from particle_simulator_b200 import Simulation, scenes
 
 pytestmark = pytest.mark.gpu
 
@@ -43,19 +45,15 @@ def test_draw_rects_and_rainbow_colors(precision, collisions):
         sim.rainbow_colors()
         cols = sim.get_colors()
     assert np.array_equal(rects.view(np.uint32), rects_reference(pos, scene.radius).view(np.uint32))
-    p = core.Particles.init(scene.count, scene.radius)
-    core.Spawner.assignRainbowColors(p)
-    assert np.array_equal(cols, p.colors)
+    assert np.array_equal(cols, colors_ref.assign_rainbow_colors(scene.count))
 
 
-def test_rainbow_colors_odd_count_matches_host_mirror():
+def test_rainbow_colors_odd_count_matches_the_oracle():
     scene = scenes.Scene(count=36_001, width=500.0, height=400.0)
     with Simulation(scene, collisions=False) as sim:
         sim.rainbow_colors()
         cols = sim.get_colors()
-    p = core.Particles.init(scene.count, scene.radius)
-    core.Spawner.assignRainbowColors(p)
-    assert np.array_equal(cols, p.colors)
+    assert np.array_equal(cols, colors_ref.assign_rainbow_colors(scene.count))
 
 
 def test_headless_frame_matches_index_order_painter():
