@@ -105,14 +105,16 @@ struct DevState {
     uint32_t trace_ns[64];     // nanoseconds since the kernel's first round
 };
 __device__ __forceinline__ unsigned long long global_ns() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
-constexpr uint32_t FLAG_CELL_OVERFLOW = 1u, FLAG_CAPACITY = 2u, FLAG_CORRUPT = 4u;
+constexpr uint32_t FLAG_CELL_OVERFLOW = 1u, FLAG_CAPACITY = 2u, FLAG_CORRUPT = 4u, FLAG_LIST_TOO_LONG = 8u;
 
-// contact-list entry: partner slot (28 bits) | role (bit 31: 1 = this particle is the centre).  The offset index is not
-// stored: a partner from another cell appears once in a sub-list, a partner from the own cell twice with opposite roles
-// (SURVEY Q1), so partner + role identify the entry.
+// contact-list entry: partner slot (bits 0..27) | role (bit 28: 1 = this particle is the centre).  The offset index is
+// not stored: a partner from another cell appears once in a sub-list, a partner from the own cell twice with opposite
+// roles, so partner + role identify the entry.  29 bits, so that an entry fits the per-particle head word.
 constexpr uint32_t ENT_SLOT_MASK = (1u << 28) - 1;
-constexpr uint32_t ENT_CENTRE = 1u << 31;
-__device__ __forceinline__ uint32_t make_entry(uint32_t partner, uint32_t /*o*/, uint32_t centre) { return partner | (centre << 31); }
+constexpr int ENT_ROLE_BIT = 28;
+constexpr uint32_t ENT_CENTRE = 1u << ENT_ROLE_BIT;
+constexpr uint32_t ENT_MASK = (1u << 29) - 1;
+__device__ __forceinline__ uint32_t make_entry(uint32_t partner, uint32_t /*o*/, uint32_t centre) { return partner | (centre << ENT_ROLE_BIT); }
 
 // x / grid_size (src/core.zig:104-105).  When grid_size is a power of two (the reference's 4.0) the quotient equals
 // x * (1 / grid_size) bit for bit (scaling by a power of two is exact), which spares the IEEE division sequence.
@@ -336,19 +338,37 @@ __device__ __forceinline__ void walk_contacts(uint32_t a, const Rec<Real>* __res
     if (s.right) seg(s.r0, s.r1, 4u, 0u);
 }
 
-// Per-particle cursor word, one 64-bit value so that a reader always sees a consistent snapshot:
-//   bits 63..45  stamp  = 1 + round of the last advance (0 = not advanced yet)
-//   bits 44..32  rem    = entries of this particle's sub-list not yet executed (<= 8191)
-//   bits 31..0   cursor = index in `entries` of the sub-list's current head
+// Per-particle resolve state, 16 bytes, read and written with one 128-bit access:
+//   head    one 64-bit word, so that a reader always sees a consistent snapshot of
+//             bits 63..45  stamp = 1 + round of the last advance (0 = not advanced yet)
+//             bits 44..32  rem   = entries of this particle's sub-list not yet executed (<= 8191)
+//             bits 28..0   entry = the sub-list's current head entry (partner slot + role), valid when rem > 0
+//   cursor  index in `entries` of the current head entry
+//   next    the entry after the head (valid when rem > 1)
+// Whether a pair is ready is decided from the two `head` words alone (no dependent load of the entry itself); `cursor`
+// and `next` are only used by the one thread that runs the pair, which by then knows that nobody else is changing the
+// particle (only the thread that runs a particle's head pair ever writes its state).
+struct __align__(16) PState { unsigned long long head; uint32_t cursor, next; };
 constexpr int HEAD_REM_BITS = 13;
 constexpr uint32_t HEAD_REM_MAX = (1u << HEAD_REM_BITS) - 1;
 constexpr uint32_t HEAD_STAMP_MAX = (1u << (32 - HEAD_REM_BITS)) - 1;
-__host__ __device__ __forceinline__ unsigned long long head_word(uint32_t stamp, uint32_t rem, uint32_t cursor) {
-    return ((unsigned long long)stamp << (32 + HEAD_REM_BITS)) | ((unsigned long long)rem << 32) | cursor;
+__host__ __device__ __forceinline__ unsigned long long head_word(uint32_t stamp, uint32_t rem, uint32_t entry) {
+    return ((unsigned long long)stamp << (32 + HEAD_REM_BITS)) | ((unsigned long long)rem << 32) | entry;
 }
 __device__ __forceinline__ uint32_t head_stamp(unsigned long long h) { return (uint32_t)(h >> (32 + HEAD_REM_BITS)); }
 __device__ __forceinline__ uint32_t head_rem(unsigned long long h) { return (uint32_t)(h >> 32) & HEAD_REM_MAX; }
-__device__ __forceinline__ uint32_t head_cursor(unsigned long long h) { return (uint32_t)h; }
+__device__ __forceinline__ uint32_t head_entry(unsigned long long h) { return (uint32_t)h & ENT_MASK; }
+__device__ __forceinline__ PState ld_state(const PState* p) {
+    const uint4 v = *reinterpret_cast<const uint4*>(p);
+    return PState{(unsigned long long)v.x | ((unsigned long long)v.y << 32), v.z, v.w};
+}
+__device__ __forceinline__ PState ld_state_cg(const PState* p) {
+    const uint4 v = __ldcg(reinterpret_cast<const uint4*>(p));
+    return PState{(unsigned long long)v.x | ((unsigned long long)v.y << 32), v.z, v.w};
+}
+__device__ __forceinline__ void st_state(PState* p, unsigned long long head, uint32_t cursor, uint32_t next) {
+    *reinterpret_cast<uint4*>(p) = make_uint4((uint32_t)head, (uint32_t)(head >> 32), cursor, next);
+}
 
 // One kernel builds every particle's contact sub-list.  Each candidate of the 3x3 block is tested
 // ONCE (three flat loops over the contiguous slot ranges of the left, own and right column) and the
@@ -529,14 +549,14 @@ __device__ __forceinline__ uint32_t list_mask(uint32_t hits, const Stencil& st, 
     return left | mid | right;
 }
 
-// Write the entries of a list-ordered mask; returns the first one.  Entry of list bit p in run i = base_i + p with
-// base_i = (first slot of the run - start of the run) + role bit, all modulo 2^32.
-__device__ __forceinline__ uint32_t emit_list(uint32_t lm, const Stencil& st, uint32_t a, const ListRuns& r,
-                                              uint32_t* __restrict__ entries, uint32_t w) {
+// Write the entries of a list-ordered mask; returns the first two (.x, .y; 0 where there is none).  Entry of list bit p
+// in run i = base_i + p with base_i = (first slot of the run - start of the run) + role bit, all modulo 2^32.
+__device__ __forceinline__ uint2 emit_list(uint32_t lm, const Stencil& st, uint32_t a, const ListRuns& r,
+                                           uint32_t* __restrict__ entries, uint32_t w) {
     const uint32_t b0 = st.l0, b1 = st.m0 - r.t1, b2 = st.m1 - r.t2 + ENT_CENTRE, b3 = a + 1u - r.t3 + ENT_CENTRE,
                    b4 = st.r1 - r.t4 + ENT_CENTRE, b5 = st.l2 - r.t5 + ENT_CENTRE, b6 = a + 1u - r.t6, b7 = st.r0 - r.t7;
-    uint32_t first = 0u;
-    bool have = false;
+    uint2 head2 = make_uint2(0u, 0u);
+    uint32_t k = 0;
     while (lm) {
         const uint32_t p = (uint32_t)__ffs((int)lm) - 1u;
         lm &= lm - 1u;
@@ -544,15 +564,16 @@ __device__ __forceinline__ uint32_t emit_list(uint32_t lm, const Stencil& st, ui
         const uint32_t hi = p < r.t6 ? (p < r.t5 ? b4 : b5) : (p < r.t7 ? b6 : b7);
         const uint32_t e = (p < r.t4 ? lo : hi) + p;
         entries[w++] = e;
-        if (!have) { first = e; have = true; }
+        if (k == 0) head2.x = e; else if (k == 1) head2.y = e;
+        ++k;
     }
-    return first;
+    return head2;
 }
 
 template <class Real, bool SLAB>
 __global__ void __launch_bounds__(DETECT_THREADS, (sizeof(Real) == 4 ? PS_DETECT_MINB : 4) * 256 / DETECT_THREADS)   // 40 / 64 registers: more resident warps to hide the load latency
 detect_kernel(const Rec<Real>* __restrict__ rec, const uint32_t* __restrict__ cell_start, uint32_t n, StepConst<Real> k,
-              uint32_t* __restrict__ entries, uint32_t entries_cap, unsigned long long* __restrict__ head,
+              uint32_t* __restrict__ entries, uint32_t entries_cap, PState* __restrict__ state,
               uint2* __restrict__ wl0, DevState* __restrict__ ds, SlabView sv) {
     __shared__ uint32_t sh_base, sh_wbase;
     const uint32_t a = blockIdx.x * blockDim.x + threadIdx.x;
@@ -560,11 +581,10 @@ detect_kernel(const Rec<Real>* __restrict__ rec, const uint32_t* __restrict__ ce
     // requested before that count is known (any slot below the capacity may be read), so the two loads overlap.
     const auto pa = a < n ? ld_pos(rec + a) : decltype(ld_pos(rec)){};
     if (SLAB) n = *sv.n_local;
-    const bool valid = a < n;
-    if (ds->flags) {                                         // error state (uniform: set by an earlier launch): no lists, no resolve
-        if (valid) head[a] = 0ull;
-        return;
-    }
+    // Error state: no lists, no resolve.  The flag can also be raised by another CTA of this launch, so threads of one CTA
+    // may disagree about it: nobody leaves before the CTA-wide scan and its barrier, dead threads just contribute nothing.
+    const bool dead = ds->flags != 0u;
+    const bool valid = a < n && !dead;
     Stencil st{};
     uint32_t cnt = 0, nL = 0, nM = 0;
     uint32_t m32 = 0u;
@@ -630,20 +650,22 @@ detect_kernel(const Rec<Real>* __restrict__ rec, const uint32_t* __restrict__ ce
         sh_wbase = tw ? atomicAdd(&ds->wl_count[0], tw) : 0u;
     }
     __syncthreads();
-    if (!valid) return;
+    if (!valid) {
+        if (dead && a < n) st_state(state + a, 0ull, 0u, 0u);
+        return;
+    }
     const uint32_t te = total & ((1u << 22) - 1);
     const uint32_t begin = sh_base + (ex & ((1u << 22) - 1));
     if ((uint64_t)sh_base + te > entries_cap || cnt > HEAD_REM_MAX) {   // does not fit: flag; the resolve kernel will not run
-        atomicOr(&ds->flags, FLAG_CAPACITY);
-        head[a] = 0ull;
+        atomicOr(&ds->flags, cnt > HEAD_REM_MAX ? FLAG_LIST_TOO_LONG : FLAG_CAPACITY);
+        st_state(state + a, 0ull, 0u, 0u);
         return;
     }
-    head[a] = head_word(0u, blocked ? 0u : cnt, begin);
     if (SLAB && blocked) sv.brem[a] = cnt;                   // brem is zero everywhere else (cleared at creation and by the unblock kernel)
-    if (!cnt) return;
-    uint32_t first_entry;
+    if (!cnt) { st_state(state + a, 0ull, begin, 0u); return; }
+    uint2 head2;
     if (path == 0) {
-        first_entry = emit_list(m32, st, a, list_runs(st, a), entries, begin);
+        head2 = emit_list(m32, st, a, list_runs(st, a), entries, begin);
     } else if (path == 1) {
         emit_block<unsigned long long>(m64, st, a, nL, nM, own, entries, begin);
     } else {
@@ -653,8 +675,9 @@ detect_kernel(const Rec<Real>* __restrict__ rec, const uint32_t* __restrict__ ce
             if (keep) entries[w++] = make_entry(q, o, centre);
         });
     }
-    if (path != 0) first_entry = entries[begin];
-    if (listed) wl0[sh_wbase + (ex >> 22)] = make_uint2(a, first_entry);
+    if (path != 0) head2 = make_uint2(entries[begin], cnt > 1u ? entries[begin + 1u] : 0u);
+    st_state(state + a, head_word(0u, blocked ? 0u : cnt, head2.x), begin, head2.y);
+    if (listed) wl0[sh_wbase + (ex >> 22)] = make_uint2(a, head2.x);
 }
 
 
@@ -698,7 +721,8 @@ __device__ __forceinline__ void resolve_pair(Rec<Real>& I, Rec<Real>& J, const S
     const Real nx = div_rn(ddx, dist), ny = div_rn(ddy, dist);                // :361
     const Real rvx = J.u - I.u, rvy = J.w - I.w;                              // :363
     const Real van = rvx * nx + rvy * ny;                                     // :365
-    const Real kk = div_rn(k.k_coef * van, (Real)2);                          // :368
+    const Real kk = (k.k_coef * van) * (Real)0.5;                             // :368  `/ 2.0`: halving is exact in binary floating point, so the
+                                                                              //       product with 0.5 is the same bits as the IEEE quotient
     const Real overlap = k.min_dis - dist;                                    // :372-374
     const Real corr = overlap * (Real)0.5;                                    // :375
     if (overlap > (Real)0) {                                                  // :377
@@ -718,8 +742,8 @@ __device__ __forceinline__ void resolve_pair(Rec<Real>& I, Rec<Real>& J, const S
 
 constexpr int RESOLVE_THREADS = 1024;     // one CTA per SM in the grid phase: the grid barrier has 148 participants
 constexpr int RESOLVE_TAIL_THREADS = 256; // the single-CTA tail keeps 8 warps (a CTA barrier among 32 warps is slower)
-constexpr uint32_t RESOLVE_TAIL = 512;    // work lists this short are finished by one CTA with CTA barriers only
-constexpr uint32_t RESOLVE_SMEM_TAIL = 256; // ... and lists this short stay in shared memory between rounds (deep chains: hundreds of short rounds)
+constexpr uint32_t RESOLVE_TAIL = 512;    // work lists this short are finished by one CTA out of shared memory (deep chains: hundreds of short rounds)
+constexpr uint32_t RESOLVE_TAIL_CAP = 2 * RESOLVE_TAIL;   // a round appends at most two items per item
 
 // One work item {a, ea}: a particle whose head moved in the previous round (or any particle with a list when
 // r = 0) together with its head entry.  Runs the pair if it is ready and this thread is the one to run it; returns
@@ -729,48 +753,50 @@ constexpr uint32_t RESOLVE_SMEM_TAIL = 256; // ... and lists this short stay in 
 // rounds keeps coherent with the CTA's own writes.  Chains revisit the same few particles round after round, so the
 // L1 hits cut the per-round latency.  (Nothing was loaded through L1 earlier in the kernel, so no stale lines exist.)
 template <class Real, bool LOCAL>
-__device__ __forceinline__ int resolve_item(Rec<Real>* rec, const uint32_t* __restrict__ entries, unsigned long long* head,
+__device__ __forceinline__ int resolve_item(Rec<Real>* rec, const uint32_t* __restrict__ entries, PState* state,
                                             uint2 item, uint32_t r, const StepConst<Real>& k, uint2 (&next)[2]) {
     const uint32_t a = item.x, ea = item.y;
     const uint32_t b = ea & ENT_SLOT_MASK;
     // Round 0: every particle with a visible list is on the work list, and a pair can only be ready if the two
     // heads name each other, in which case the lower slot's thread runs it.  So the higher slot need not look.
     if (r == 0u && b < a) return 0;
-    // everything that depends only on the item is requested at once (the records speculatively)
-    const unsigned long long ha = LOCAL ? head[a] : __ldcg(head + a);
-    const unsigned long long hb = LOCAL ? head[b] : __ldcg(head + b);
+    // everything that depends only on the item is requested at once (the records speculatively): one round trip to
+    // memory decides whether the pair runs and brings what it needs
+    const PState sa = LOCAL ? ld_state(state + a) : ld_state_cg(state + a);
+    const PState sb = LOCAL ? ld_state(state + b) : ld_state_cg(state + b);
     const Rec<Real> Ra = LOCAL ? ld_rec(rec + a) : ld_rec_cg(rec + a), Rb = LOCAL ? ld_rec(rec + b) : ld_rec_cg(rec + b);
+    const unsigned long long ha = sa.head, hb = sb.head;
     if (head_stamp(ha) == r + 1) return 0;           // a already ran a pair this round (executed by its partner)
     if (head_stamp(hb) == r + 1) return 0;           // b moved this round; b is on the next list and will look at a
     const uint32_t rem_a = head_rem(ha), rem_b = head_rem(hb);
     if (rem_b == 0) return 0;                        // (rem_a > 0: a is on the list)
-    const uint32_t ia = head_cursor(ha), ib = head_cursor(hb);
-    const uint32_t eb = entries[ib];
-    const uint32_t ea_next = rem_a > 1 ? entries[ia + 1] : 0u;
-    const uint32_t eb_next = rem_b > 1 ? entries[ib + 1] : 0u;
     // same pair seen from the other side: partner = a, opposite role
-    if (eb != (a | (~ea & ENT_CENTRE))) return 0;
+    if (head_entry(hb) != (a | (~ea & ENT_CENTRE))) return 0;
     // Both particles on this round's list (b's head last moved in round r-1, or never when r = 0): the
-    // lower slot runs the pair.  Membership is read from the SAME 64-bit word as the cursor, so a
+    // lower slot runs the pair.  Membership is read from the SAME 64-bit word as the head entry, so a
     // concurrent executor cannot make the two threads disagree.
     if (b < a && head_stamp(hb) == r) return 0;
-    const bool a_centre = (ea >> 31) != 0;           // entry = {particle_i = neighbour, particle_j = centre}
+    // the entries that become `next` after the advance (requested now, needed only when the state is written back)
+    const uint32_t nn_a = rem_a > 2 ? entries[sa.cursor + 2] : 0u;
+    const uint32_t nn_b = rem_b > 2 ? entries[sb.cursor + 2] : 0u;
+    const bool a_centre = (ea >> ENT_ROLE_BIT) != 0; // entry = {particle_i = neighbour, particle_j = centre}
     Rec<Real> I = a_centre ? Rb : Ra, J = a_centre ? Ra : Rb;
     resolve_pair<Real>(I, J, k);
     st_rec(rec + (a_centre ? b : a), I);
     st_rec(rec + (a_centre ? a : b), J);
-    head[a] = head_word(r + 1, rem_a - 1, ia + 1);
-    head[b] = head_word(r + 1, rem_b - 1, ib + 1);
-    int m = 0;
-    if (rem_a > 1) next[m++] = make_uint2(a, ea_next);
-    if (rem_b > 1) next[m++] = make_uint2(b, eb_next);
-    return m;
+    st_state(state + a, head_word(r + 1, rem_a - 1, rem_a > 1 ? sa.next : 0u), sa.cursor + 1, nn_a);
+    st_state(state + b, head_word(r + 1, rem_b - 1, rem_b > 1 ? sb.next : 0u), sb.cursor + 1, nn_b);
+    const uint2 na = make_uint2(a, sa.next), nb = make_uint2(b, sb.next);
+    const bool more_a = rem_a > 1, more_b = rem_b > 1;     // (constant indices keep `next` in registers)
+    next[0] = more_a ? na : nb;
+    next[1] = nb;
+    return (more_a ? 1 : 0) + (more_b ? 1 : 0);
 }
 
 // One round over the work list `wl[0..cnt)` by one or many CTAs; appends the particles advanced in this round, with
 // their new head entry, to `out` (buffered per CTA: one global atomic per batch of 256 items).
 template <class Real>
-__device__ __forceinline__ void resolve_round(Rec<Real>* rec, const uint32_t* __restrict__ entries, unsigned long long* head,
+__device__ __forceinline__ void resolve_round(Rec<Real>* rec, const uint32_t* __restrict__ entries, PState* state,
                                               const uint2* wl, uint32_t cnt, uint2* out, uint32_t* out_count, uint32_t r,
                                               uint32_t first, uint32_t stride, uint32_t cta_threads, const StepConst<Real>& k,
                                               uint2* sh_buf, uint32_t* sh_cnt, uint32_t* sh_base) {
@@ -780,7 +806,7 @@ __device__ __forceinline__ void resolve_round(Rec<Real>* rec, const uint32_t* __
         const uint32_t idx = base + threadIdx.x;
         if (idx < cnt) {
             uint2 next[2];
-            const int m = resolve_item<Real, false>(rec, entries, head, __ldcg(wl + idx), r, k, next);
+            const int m = resolve_item<Real, false>(rec, entries, state, __ldcg(wl + idx), r, k, next);
             for (int i = 0; i < m; ++i) sh_buf[atomicAdd(sh_cnt, 1u)] = next[i];
         }
         __syncthreads();
@@ -800,7 +826,7 @@ __device__ __forceinline__ void resolve_round(Rec<Real>* rec, const uint32_t* __
 // the chain of dependent L2 round trips of one batch overlaps with those of the other warps' batches.
 constexpr uint32_t RESOLVE_WBUF = 128;   // items per warp buffer; a batch appends at most 64
 template <class Real>
-__device__ __forceinline__ void resolve_round_warps(Rec<Real>* rec, const uint32_t* __restrict__ entries, unsigned long long* head,
+__device__ __forceinline__ void resolve_round_warps(Rec<Real>* rec, const uint32_t* __restrict__ entries, PState* state,
                                                     const uint2* wl, uint32_t cnt, uint2* out, uint32_t* out_count, uint32_t r,
                                                     uint32_t first, uint32_t stride, const StepConst<Real>& k, uint2* sh_wbuf) {
     const uint32_t lane = threadIdx.x & 31u;
@@ -823,7 +849,7 @@ __device__ __forceinline__ void resolve_round_warps(Rec<Real>* rec, const uint32
         const uint32_t ahead = idx + stride;
         if (ahead < cnt) item = __ldcg(wl + ahead);
         uint2 next[2];
-        const int m = live ? resolve_item<Real, false>(rec, entries, head, cur, r, k, next) : 0;
+        const int m = live ? resolve_item<Real, false>(rec, entries, state, cur, r, k, next) : 0;
         const uint32_t one = __ballot_sync(0xffffffffu, m >= 1), two = __ballot_sync(0xffffffffu, m >= 2);
         if (one) {
             const uint32_t below = (1u << lane) - 1u;
@@ -839,12 +865,12 @@ __device__ __forceinline__ void resolve_round_warps(Rec<Real>* rec, const uint32
 
 template <class Real>
 __global__ void __launch_bounds__(RESOLVE_THREADS)
-resolve_kernel(Rec<Real>* rec, const uint32_t* __restrict__ entries, unsigned long long* head,
+resolve_kernel(Rec<Real>* rec, const uint32_t* __restrict__ entries, PState* state,
                uint2* wl0, uint2* wl1, uint2* wl2, StepConst<Real> k, DevState* ds, uint32_t r_start) {
     cg::grid_group grid = cg::this_grid();
     __shared__ uint2 sh_buf[(RESOLVE_THREADS / 32) * RESOLVE_WBUF];   // grid phase: one append buffer per warp; tail: one for the CTA
     __shared__ uint32_t sh_cnt, sh_base;
-    uint2* lists[3] = {wl0, wl1, wl2};
+    auto list = [&](uint32_t i) { return i == 0 ? wl0 : (i == 1 ? wl1 : wl2); };   // (an indexed array would live in local memory)
     const bool leader = blockIdx.x == 0 && threadIdx.x == 0;
     if (ds->flags) {                                         // uniform across the grid: set before this launch
         if (leader) ds->wl_count[0] = 0;
@@ -860,56 +886,79 @@ resolve_kernel(Rec<Real>* rec, const uint32_t* __restrict__ entries, unsigned lo
         if (trace && r < 64) { ds->trace_cnt[r] = cnt; ds->trace_ns[r] = (uint32_t)(global_ns() - t_begin); }
         if (cnt <= RESOLVE_TAIL) break;                      // same value in every thread: the whole grid leaves together
         if (leader) ds->wl_count[nn] = 0;                    // consumed in round r-1, refilled in round r+1
-        resolve_round_warps<Real>(rec, entries, head, lists[cur], cnt, lists[nxt], &ds->wl_count[nxt], r,
+        resolve_round_warps<Real>(rec, entries, state, list(cur), cnt, list(nxt), &ds->wl_count[nxt], r,
                                   blockIdx.x * RESOLVE_THREADS, gridDim.x * RESOLVE_THREADS, k, sh_buf);
         grid.sync();
     }
     if (blockIdx.x != 0 || threadIdx.x >= RESOLVE_TAIL_THREADS) return;     // exited threads count as arrived at later CTA barriers
-    // tail phase: CTA 0 alone, CTA barriers only (its own writes reach L2 before the barrier releases).  A settled
-    // pile has hundreds of short rounds whose cost is a chain of L2 round trips, so while the work list is at most
-    // RESOLVE_SMEM_TAIL items long it lives in shared memory: no list loads, no counters, no atomics in global memory.
-    __shared__ uint2 sh_items[2][2 * RESOLVE_SMEM_TAIL];
-    __shared__ uint32_t sh_n[2];
+    // Tail phase: CTA 0 alone.  A settled pile has hundreds of short rounds whose cost is the chain "read the two
+    // particles - resolve - write them back - tell the other threads", so a round here costs ONE CTA barrier and nothing
+    // else that is shared: the work list lives in shared memory (three rotating buffers carved out of the grid phase's
+    // append buffers, with their lengths beside them), items are appended with one shared-memory atomic per warp, and
+    // the particles' records and states are served by this SM's L1 (plain loads; the barrier makes the CTA's own
+    // writes visible).  A list that outgrows the buffers (rare) goes back to global memory for a round.
+    uint2* const tl_items = sh_buf;                          // [3][RESOLVE_TAIL_CAP]
+    __shared__ uint32_t tl_n[3];
+    const uint32_t lane = threadIdx.x & 31u;
     bool in_smem = false;
-    uint32_t cnt_smem = 0;
-    for (;; ++r) {
-        const uint32_t cur = r % 3, nxt = (r + 1) % 3, nn = (r + 2) % 3, sc = r & 1u, sn = sc ^ 1u;
-        uint32_t cnt = in_smem ? cnt_smem : __ldcg(&ds->wl_count[cur]);
+    for (;;) {
+        if (!in_smem) {
+            const uint32_t cur = r % 3, nxt = (r + 1) % 3, nn = (r + 2) % 3;
+            const uint32_t cnt = __ldcg(&ds->wl_count[cur]);
+            if (trace && r < 64) { ds->trace_cnt[r] = cnt; ds->trace_ns[r] = (uint32_t)(global_ns() - t_begin); }
+            if (cnt == 0 || r + 2 >= HEAD_STAMP_MAX) break;
+            __syncthreads();                                 // everyone has read the count before anything moves on
+            if (cnt <= RESOLVE_TAIL) {                       // short enough: pull the list into shared memory
+                for (uint32_t i = threadIdx.x; i < cnt; i += RESOLVE_TAIL_THREADS) tl_items[cur * RESOLVE_TAIL_CAP + i] = __ldcg(list(cur) + i);
+                if (threadIdx.x == 0) { tl_n[cur] = cnt; tl_n[nxt] = 0; }
+                in_smem = true;
+                __syncthreads();
+                continue;
+            }
+            if (threadIdx.x == 0) ds->wl_count[nn] = 0;
+            resolve_round<Real>(rec, entries, state, list(cur), cnt, list(nxt), &ds->wl_count[nxt], r,
+                                0u, RESOLVE_TAIL_THREADS, RESOLVE_TAIL_THREADS, k, sh_buf, &sh_cnt, &sh_base);
+            __threadfence();
+            __syncthreads();
+            ++r;
+            continue;
+        }
+        const uint32_t cur = r % 3, nxt = (r + 1) % 3, nn = (r + 2) % 3;
+        const uint32_t cnt = tl_n[cur];
         if (trace && r < 64) { ds->trace_cnt[r] = cnt; ds->trace_ns[r] = (uint32_t)(global_ns() - t_begin); }
         if (cnt == 0 || r + 2 >= HEAD_STAMP_MAX) break;
-        __syncthreads();                                     // everyone has read the count before anything moves on
-        if (!in_smem && cnt <= RESOLVE_SMEM_TAIL) {          // short enough: pull the list into shared memory
-            for (uint32_t i = threadIdx.x; i < cnt; i += RESOLVE_TAIL_THREADS) sh_items[sc][i] = __ldcg(lists[cur] + i);
-            in_smem = true;
-            __syncthreads();
-        } else if (in_smem && cnt > RESOLVE_SMEM_TAIL) {     // grew again (rare): push it back to the global list
-            for (uint32_t i = threadIdx.x; i < cnt; i += RESOLVE_TAIL_THREADS) lists[cur][i] = sh_items[sc][i];
+        if (cnt > RESOLVE_TAIL) {                            // grew beyond what the next round's appends could hold: back to global memory
+            for (uint32_t i = threadIdx.x; i < cnt; i += RESOLVE_TAIL_THREADS) list(cur)[i] = tl_items[cur * RESOLVE_TAIL_CAP + i];
             if (threadIdx.x == 0) { ds->wl_count[cur] = cnt; ds->wl_count[nxt] = 0; }
             in_smem = false;
             __threadfence();
             __syncthreads();
+            continue;
         }
-        if (in_smem) {
-            if (threadIdx.x == 0) sh_n[sn] = 0;
-            __syncthreads();
-            if (threadIdx.x < cnt) {                         // cnt <= RESOLVE_SMEM_TAIL <= RESOLVE_TAIL_THREADS: one item per thread
-                uint2 next[2];
-                const int m = resolve_item<Real, true>(rec, entries, head, sh_items[sc][threadIdx.x], r, k, next);
-                for (int i = 0; i < m; ++i) sh_items[sn][atomicAdd(&sh_n[sn], 1u)] = next[i];
+        if (threadIdx.x == 0) tl_n[nn] = 0;                  // the input of round r-1; everybody read it before that round's barrier
+        const uint2* in = tl_items + cur * RESOLVE_TAIL_CAP;
+        uint2* out = tl_items + nxt * RESOLVE_TAIL_CAP;
+        for (uint32_t idx = threadIdx.x; idx - lane < cnt; idx += RESOLVE_TAIL_THREADS) {   // whole warps: the ballots below need every lane
+            uint2 next[2];
+            const int m = idx < cnt ? resolve_item<Real, true>(rec, entries, state, in[idx], r, k, next) : 0;
+            const uint32_t one = __ballot_sync(0xffffffffu, m >= 1), two = __ballot_sync(0xffffffffu, m >= 2);
+            if (one) {
+                uint32_t base = 0;
+                if (lane == 0) base = atomicAdd(&tl_n[nxt], (uint32_t)__popc(one) + (uint32_t)__popc(two));
+                base = __shfl_sync(0xffffffffu, base, 0);
+                const uint32_t below = (1u << lane) - 1u;
+                const uint32_t at = base + (uint32_t)__popc(one & below) + (uint32_t)__popc(two & below);
+                if (m >= 1) out[at] = next[0];
+                if (m >= 2) out[at + 1] = next[1];
             }
-            __syncthreads();                                 // makes this round's global writes visible to the whole CTA
-            cnt_smem = sh_n[sn];                             // at most 2 * cnt items: fits the buffer
-        } else {
-            if (threadIdx.x == 0) ds->wl_count[nn] = 0;
-            resolve_round<Real>(rec, entries, head, lists[cur], cnt, lists[nxt], &ds->wl_count[nxt], r,
-                                0u, RESOLVE_TAIL_THREADS, RESOLVE_TAIL_THREADS, k, sh_buf, &sh_cnt, &sh_base);
-            __threadfence();
-            __syncthreads();
         }
+        __syncthreads();                                     // the round's one barrier: global writes and appended items become visible
+        ++r;
     }
-    const bool stamps_exhausted = (in_smem ? cnt_smem : __ldcg(&ds->wl_count[r % 3])) != 0;
+    uint32_t left = 0;
+    if (threadIdx.x == 0) left = in_smem ? tl_n[r % 3] : __ldcg(&ds->wl_count[r % 3]);
     if (threadIdx.x == 0) {
-        if (stamps_exhausted) atomicOr(&ds->flags, FLAG_CAPACITY);          // ran out of round stamps (never in practice)
+        if (left != 0) atomicOr(&ds->flags, FLAG_CAPACITY);          // ran out of round stamps (never in practice)
         ds->rounds_last = r;
         if (trace) ds->trace_rounds = r < 63 ? r + 1 : 64;
         ds->rounds_total += r - r_start;
@@ -940,7 +989,7 @@ struct Collider {
     uint32_t* pid[2] = {nullptr, nullptr};
     uint32_t *ctr_count = nullptr, *ctr_off = nullptr;
     uint32_t* entries = nullptr; uint32_t entries_cap = 0;
-    unsigned long long* head = nullptr;
+    PState* state = nullptr;
     uint2* wl[3] = {nullptr, nullptr, nullptr};
     uint64_t* pairs = nullptr; uint32_t pairs_cap = 0;
     DevState* ds = nullptr;
@@ -970,7 +1019,7 @@ struct Collider {
             if ((rc = alloc(&pid[i], n, err))) return rc;
         }
         if ((rc = alloc(&entries, (uint64_t)entries_cap, err))) return rc;
-        if ((rc = alloc(&head, n, err))) return rc;
+        if ((rc = alloc(&state, n, err))) return rc;
         for (int i = 0; i < 3; ++i) if ((rc = alloc(&wl[i], n, err))) return rc;
         if ((rc = alloc(&ds, 1, err))) return rc;
         PS_CUDA_TRY(err, cudaMemsetAsync(ds, 0, sizeof(DevState), st));
@@ -987,7 +1036,7 @@ struct Collider {
 
     void destroy() {
         cudaFree(cell_count); cudaFree(cell_start); cudaFree(scan_sums); cudaFree(slot_cell); cudaFree(arrival);
-        cudaFree(tmp_id); cudaFree(ctr_count); cudaFree(ctr_off); cudaFree(entries); cudaFree(head);
+        cudaFree(tmp_id); cudaFree(ctr_count); cudaFree(ctr_off); cudaFree(entries); cudaFree(state);
         for (auto& r : rec) cudaFree(r);
         for (auto& p : pid) cudaFree(p);
         for (auto& w : wl) cudaFree(w);
@@ -1037,7 +1086,7 @@ struct Collider {
         PS_CUDA_TRY(err, exclusive_scan<uint8_t>(reinterpret_cast<const uint8_t*>(cell_count), cell_start, ncell, scan_sums, cell_start + ncell, &ds->max_cell, st));
         place_kernel<<<(gn + SORT_ILP - 1) / SORT_ILP, 256, 0, st>>>(slot_cell, arrival, pid[cur], cell_start, n32, tmp_id);
         move_kernel<Real><<<(gn + SORT_ILP - 1) / SORT_ILP, 256, 0, st>>>(rec[cur], pid[cur], slot_cell, cell_start, tmp_id, n32, k, rec[nw], pid[nw], ds);
-        detect_kernel<Real, false><<<(unsigned)((n + DETECT_THREADS - 1) / DETECT_THREADS), DETECT_THREADS, 0, st>>>(rec[nw], cell_start, n32, k, entries, entries_cap, head, wl[0], ds, SlabView{});
+        detect_kernel<Real, false><<<(unsigned)((n + DETECT_THREADS - 1) / DETECT_THREADS), DETECT_THREADS, 0, st>>>(rec[nw], cell_start, n32, k, entries, entries_cap, state, wl[0], ds, SlabView{});
         *launches += 7;
         if (capture) {
             count_centre_kernel<Real><<<gn, 256, 0, st>>>(rec[nw], cell_start, n32, k, ctr_count);
@@ -1047,7 +1096,7 @@ struct Collider {
         }
         {
             Rec<Real>* a_rec = rec[nw]; const uint32_t* a_ent = entries;
-            unsigned long long* a_head = head; uint2 *a0 = wl[0], *a1 = wl[1], *a2 = wl[2];
+            PState* a_head = state; uint2 *a0 = wl[0], *a1 = wl[1], *a2 = wl[2];
             StepConst<Real> a_k = k; DevState* a_ds = ds; uint32_t a_r0 = 0;
             void* args[] = {&a_rec, &a_ent, &a_head, &a0, &a1, &a2, &a_k, &a_ds, &a_r0};
             const uint64_t want = (n + RESOLVE_THREADS - 1) / RESOLVE_THREADS;
@@ -1064,6 +1113,11 @@ struct Collider {
         DevState h{};
         PS_CUDA_TRY(err, cudaMemcpyAsync(&h, ds, sizeof(DevState), cudaMemcpyDeviceToHost, st));
         PS_CUDA_TRY(err, cudaStreamSynchronize(st));
+        if (h.flags & FLAG_LIST_TOO_LONG) {
+            err.status = PS_ERR_CAPACITY;
+            err.text = "one particle has more than 8191 contacts (the per-particle limit of the cursor word); the scene is far denser than the reference's u8 cell counters allow";
+            return err.status;
+        }
         if (h.flags & FLAG_CAPACITY) {
             err.status = PS_ERR_CAPACITY;
             err.text = "contact list exceeded its capacity (" + std::to_string(entries_cap) + " entries); raise ps_config.contacts_per_particle";

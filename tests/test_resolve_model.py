@@ -2,8 +2,8 @@
 
 The reference resolves its ordered pair list front to back (src/core.zig:211-213).  The kernel instead runs, round
 after round, every pair that heads BOTH of its particles' sub-lists, from work lists that hold only the particles whose
-head moved in the previous round.  This file restates that protocol in Python — same cursor word (stamp, entries left,
-cursor), same tie-break, same rule for the first work list — executes the items of every round in a random order, and
+head moved in the previous round.  This file restates that protocol in Python — same per-particle state (stamp, entries left,
+head entry in one word; cursor and look-ahead entry beside it), same tie-break, same rule for the first work list — executes the items of every round in a random order, and
 checks that the state ends bit-identical to the sequential loop.  Arithmetic: oracle/core_ref.py's resolve_collision.
 """
 from __future__ import annotations
@@ -29,9 +29,17 @@ def sublists(pairs, slot_of, n):
 
 
 def run_rounds(lists, execute, rng):
-    """The rounds of resolve_kernel.  execute(i_slot, j_slot) resolves one pair {i = neighbour, j = centre}."""
+    """The rounds of resolve_kernel.  execute(i_slot, j_slot) resolves one pair {i = neighbour, j = centre}.
+
+    Per particle, as in the kernel's 16-byte state: [stamp, entries left, head entry] (one 64-bit word, the only thing a
+    readiness test looks at) plus cursor and the entry after the head (touched only by the thread that runs the pair)."""
     n = len(lists)
-    head = [[0, len(l), 0] for l in lists]                       # stamp, entries left, cursor
+    entries, begin = [], []
+    for l in lists:                                              # `entries`: the sub-lists back to back, as detect lays them out
+        begin.append(len(entries))
+        entries.extend(l)
+    none = (0, 0)
+    state = [[0, len(l), l[0] if l else none, begin[a], l[1] if len(l) > 1 else none] for a, l in enumerate(lists)]
     # detect_kernel: on the first list only if the first partner has a higher slot (round 0 runs pairs from the lower slot)
     work = [(a, lists[a][0]) for a in range(n) if lists[a] and lists[a][0][0] > a]
     r, executed = 0, 0
@@ -42,26 +50,28 @@ def run_rounds(lists, execute, rng):
             b, a_centre = ea
             if r == 0 and b < a:
                 continue
-            sa, rem_a, cur_a = head[a]
-            sb, rem_b, cur_b = head[b]
+            sa, rem_a, head_a, cur_a, next_a = state[a]
+            sb, rem_b, head_b, cur_b, next_b = state[b]
             if sa == r + 1 or sb == r + 1 or rem_b == 0:
                 continue
-            if lists[b][cur_b] != (a, 1 - a_centre):             # not the same pair seen from the other side
+            if head_b != (a, 1 - a_centre):                      # not the same pair seen from the other side
                 continue
             if b < a and sb == r:                                # both on this round's list: the lower slot runs it
                 continue
-            assert lists[a][cur_a] == ea
+            assert head_a == ea and entries[cur_a] == ea and entries[cur_b] == head_b
+            nn_a = entries[cur_a + 2] if rem_a > 2 else none     # the entries that become `next` after the advance
+            nn_b = entries[cur_b + 2] if rem_b > 2 else none
             execute(b, a) if a_centre else execute(a, b)
             executed += 1
-            head[a] = [r + 1, rem_a - 1, cur_a + 1]
-            head[b] = [r + 1, rem_b - 1, cur_b + 1]
+            state[a] = [r + 1, rem_a - 1, next_a if rem_a > 1 else none, cur_a + 1, nn_a]
+            state[b] = [r + 1, rem_b - 1, next_b if rem_b > 1 else none, cur_b + 1, nn_b]
             if rem_a > 1:
-                nxt.append((a, lists[a][cur_a + 1]))
+                nxt.append((a, next_a))
             if rem_b > 1:
-                nxt.append((b, lists[b][cur_b + 1]))
+                nxt.append((b, next_b))
         work = nxt
         r += 1
-    assert all(h[1] == 0 for h in head), "some sub-list was not drained"
+    assert all(st[1] == 0 for st in state), "some sub-list was not drained"
     return r, executed
 
 

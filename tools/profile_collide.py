@@ -23,9 +23,12 @@ ap.add_argument("--warm-frames", type=int, default=1)
 ap.add_argument("--frames", type=int, default=1)
 ap.add_argument("--gravity", action="store_true")
 ap.add_argument("--spawn-on-device", action="store_true")
+ap.add_argument("--default-scene", action="store_true", help="main.zig's 13 000-particle 720x640 scene instead of a scaled square world")
 args = ap.parse_args()
 
-scene = scenes.scaled_scene(args.particles)
+scene = scenes.default_scene() if args.default_scene else scenes.scaled_scene(args.particles)
+if args.default_scene:
+    args.particles = scene.count
 dt = np.float32 if args.precision == "f32" else np.float64
 n = args.particles
 if not args.spawn_on_device:
