@@ -40,7 +40,9 @@ typedef enum ps_status {
     PS_ERR_CUDA = -3,          /* any other CUDA runtime error; text in ps_last_error */
     PS_ERR_NCCL = -4,          /* reserved for the multi-GPU slab path */
     PS_ERR_CELL_OVERFLOW = -5, /* a grid cell held > 255 particles: the reference's u8 counter would wrap or panic (src/core.zig:51,132) */
-    PS_ERR_CAPACITY = -6,      /* contact list larger than the configured capacity; state is left at the failing sub-step's post-bounce point */
+    PS_ERR_CAPACITY = -6,      /* contact list larger than the configured capacity; state is left at the failing sub-step's post-bounce point.
+                                  Like PS_ERR_CELL_OVERFLOW it is sticky: every later step returns it, until ps_upload / ps_spawn
+                                  gives the handle a new state (which clears it) */
     PS_ERR_NO_DEVICE = -7,     /* no CUDA device / library built without one: the product has no CPU path */
     PS_ERR_MIGRATION = -8      /* slab path: a particle crossed a whole neighbouring slab in one sub-step */
 } ps_status;
@@ -201,14 +203,16 @@ int ps_compute_start_array(const uint32_t* grid_array, uint32_t* start_array, ui
  * variant computes exactly what ps_compute_start_array computes and calls no allocator of any kind:
  * its partial sums go to a 64 KiB array built into the library image (every GPU that loads the
  * library holds that array until the process exits).
- *   - limit: cells <= 67 108 864 (16 384 tiles of 4096 cells); larger sizes return PS_ERR_CAPACITY
- *     with a message in ps_last_error(NULL) and touch nothing.
- *   - the first call on each device looks up the array's device address; make that first call with
- *     the device current and before starting any stream capture.
+ *   - limit: cells <= PS_STATIC_SCAN_MAX_CELLS = 67 108 864 (16 384 tiles of 4096 cells); larger sizes return
+ *     PS_ERR_CAPACITY with a message in ps_last_error(NULL) and touch nothing.
+ *   - the first call on each device looks up the array's device address and remembers it; make that first call
+ *     with the device current and before starting any stream capture.  The remembered address does not survive
+ *     cudaDeviceReset(): a process that resets a device must not call this entry point on it afterwards.
  *   - all calls on a device share the one array.  Nothing in it has to be cleared between calls (each
  *     call overwrites what it later reads), but two calls that overlap on the GPU — different streams,
  *     or different threads — race on it and both results are undefined.  Calls on one stream are safe.
  * Inputs and outputs are the caller's, as for ps_compute_start_array; in-place use is allowed. */
+#define PS_STATIC_SCAN_MAX_CELLS 67108864ull
 int ps_compute_start_array_static(const uint32_t* grid_array, uint32_t* start_array, uint64_t cells, void* cuda_stream);
 
 /* ---- one scene across the GPUs of one box (collision scenes) ------------------------

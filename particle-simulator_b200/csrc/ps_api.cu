@@ -147,7 +147,7 @@ struct SimT final : ps_sim {
         if (rc != PS_OK) return rc;
         if (vel) rc = host_f64 ? upload_one((const double*)vel, vx, vy) : upload_one((const float*)vel, vx, vy);
         if (rc != PS_OK) return rc;
-        if (cfg.collisions && (pos || vel)) col.invalidate_records();
+        if (cfg.collisions && (pos || vel)) { col.invalidate_records(); PS_CUDA_TRY(err, col.clear_flags(stream)); err = Error{}; }
         // the caller may reuse or free its buffers as soon as we return
         PS_CUDA_TRY(err, cudaStreamSynchronize(stream));
         return PS_OK;
@@ -431,7 +431,7 @@ struct SimT final : ps_sim {
         ps::spawn_soa_kernel<Real><<<148 * 16, 256, 0, stream>>>(n, z, cfg.radius, cfg.width, cfg.height, vmin, vmax, px, py, vx, vy);
         ++launches;
         PS_CUDA_TRY(err, cudaGetLastError());
-        if (cfg.collisions) col.invalidate_records();
+        if (cfg.collisions) { col.invalidate_records(); PS_CUDA_TRY(err, col.clear_flags(stream)); err = Error{}; }
         PS_CUDA_TRY(err, cudaStreamSynchronize(stream));
         return PS_OK;
     }
@@ -859,7 +859,7 @@ const char* ps_slabgroup_last_error(const ps_slabgroup* g) { return g ? g->last_
 // obtained at call time.  64 KiB per GPU that loads this library, held until the process exits.
 // One word per 4096-cell tile => at most PS_STATIC_SCAN_MAX_CELLS cells per call.
 #define PS_STATIC_SCAN_MAX_TILES 16384u
-#define PS_STATIC_SCAN_MAX_CELLS ((uint64_t)PS_STATIC_SCAN_MAX_TILES * (uint64_t)ps::SCAN_TILE)   /* 67 108 864 */
+static_assert(PS_STATIC_SCAN_MAX_CELLS == (uint64_t)PS_STATIC_SCAN_MAX_TILES * (uint64_t)ps::SCAN_TILE, "header and scratch array disagree");
 static __device__ __align__(256) uint32_t g_static_scan_sums[PS_STATIC_SCAN_MAX_TILES];
 
 namespace {

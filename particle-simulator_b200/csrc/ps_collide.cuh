@@ -91,12 +91,12 @@ __device__ __forceinline__ double floor_r(double x) { return floor(x); }
 struct DevState {
     uint32_t flags;            // bit0: cell overflow (>255), bit1: contact capacity exceeded
     uint32_t max_cell;         // running maximum cell population
-    uint32_t entries_used;     // contact-list entries allocated by detect in this sub-step (= 2 * pairs)
+    uint32_t entries_used;     // contact-list entries written by detect in this sub-step (= 2 * pairs)
     uint32_t inc_total;        // entries_used of the last completed sub-step
     uint32_t ctr_total;        // pairs of this sub-step (pair capture only)
     uint32_t wl_count[3];      // rotating work-list lengths
     uint32_t rounds_last;
-    uint32_t pad;
+    uint32_t pool_used;        // words of the overflow pool handed out in this sub-step (sub-lists longer than 1 + LIST_CHUNK)
     unsigned long long pairs_total, rounds_total;
     uint32_t dbg[4];           // first offending slot / cell when FLAG_CORRUPT is raised
     uint32_t trace_on;         // PS_RESOLVE_TRACE: record the length and start time of every resolve round
@@ -107,13 +107,19 @@ struct DevState {
 __device__ __forceinline__ unsigned long long global_ns() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
 constexpr uint32_t FLAG_CELL_OVERFLOW = 1u, FLAG_CAPACITY = 2u, FLAG_CORRUPT = 4u, FLAG_LIST_TOO_LONG = 8u;
 
-// contact-list entry: partner slot (bits 0..27) | role (bit 28: 1 = this particle is the centre).  The offset index is
-// not stored: a partner from another cell appears once in a sub-list, a partner from the own cell twice with opposite
-// roles, so partner + role identify the entry.  29 bits, so that an entry fits the per-particle head word.
+// Contact sub-lists.  Every particle's sub-list is the sequence of pair-list entries that mention it, in list order.
+//   entry word   partner slot (bits 0..27) | role (bit 28: 1 = this particle is the centre) | LAST (bit 29: final entry of
+//                the sub-list).  The offset index is not stored: a partner from another cell appears once in a sub-list, a
+//                partner from the own cell twice with opposite roles, so partner + role identify the entry.
+//   where        entry 0 lives in the particle's head word (below); entries 1..8 in the particle's own chunk of LIST_CHUNK
+//                words at a fixed place (chunks[slot * 8 ..]), so most lists need no allocation, no prefix sum and no
+//                cursor; a longer list keeps entries 1..7 in the chunk, the index of its overflow run in the pool in chunk
+//                word 7, and entries 8.. in that run (one atomic per such particle).
 constexpr uint32_t ENT_SLOT_MASK = (1u << 28) - 1;
 constexpr int ENT_ROLE_BIT = 28;
 constexpr uint32_t ENT_CENTRE = 1u << ENT_ROLE_BIT;
-constexpr uint32_t ENT_MASK = (1u << 29) - 1;
+constexpr uint32_t ENT_LAST = 1u << 29;
+constexpr uint32_t LIST_CHUNK = 8;
 __device__ __forceinline__ uint32_t make_entry(uint32_t partner, uint32_t /*o*/, uint32_t centre) { return partner | (centre << ENT_ROLE_BIT); }
 
 // x / grid_size (src/core.zig:104-105).  When grid_size is a power of two (the reference's 4.0) the quotient equals
@@ -178,7 +184,7 @@ bin_kernel(const Rec<Real>* __restrict__ rec_old, uint32_t n, StepConst<Real> k,
            uint32_t* __restrict__ slot_cell, uint32_t* __restrict__ arrival, DevState* __restrict__ ds) {
     // SORT_ILP slots per thread, CTA-strided: the loads, then the counting atomics, of all of them are in flight together
     const uint32_t s0 = blockIdx.x * (blockDim.x * SORT_ILP) + threadIdx.x;
-    if (s0 == 0) ds->entries_used = 0;                          // detect of this sub-step allocates from zero
+    if (s0 == 0) { ds->entries_used = 0; ds->pool_used = 0; }   // detect of this sub-step counts and allocates from zero
     Rec<Real> r[SORT_ILP];
     uint32_t c[SORT_ILP], a[SORT_ILP];
 #pragma unroll
@@ -338,50 +344,49 @@ __device__ __forceinline__ void walk_contacts(uint32_t a, const Rec<Real>* __res
     if (s.right) seg(s.r0, s.r1, 4u, 0u);
 }
 
-// Per-particle resolve state, 16 bytes, read and written with one 128-bit access:
-//   head    one 64-bit word, so that a reader always sees a consistent snapshot of
-//             bits 63..45  stamp = 1 + round of the last advance (0 = not advanced yet)
-//             bits 44..32  rem   = entries of this particle's sub-list not yet executed (<= 8191)
-//             bits 28..0   entry = the sub-list's current head entry (partner slot + role), valid when rem > 0
-//   cursor  index in `entries` of the current head entry
-//   next    the entry after the head (valid when rem > 1)
-// Whether a pair is ready is decided from the two `head` words alone (no dependent load of the entry itself); `cursor`
-// and `next` are only used by the one thread that runs the pair, which by then knows that nobody else is changing the
-// particle (only the thread that runs a particle's head pair ever writes its state).
-struct __align__(16) PState { unsigned long long head; uint32_t cursor, next; };
-constexpr int HEAD_REM_BITS = 13;
-constexpr uint32_t HEAD_REM_MAX = (1u << HEAD_REM_BITS) - 1;
-constexpr uint32_t HEAD_STAMP_MAX = (1u << (32 - HEAD_REM_BITS)) - 1;
-__host__ __device__ __forceinline__ unsigned long long head_word(uint32_t stamp, uint32_t rem, uint32_t entry) {
-    return ((unsigned long long)stamp << (32 + HEAD_REM_BITS)) | ((unsigned long long)rem << 32) | entry;
+// Per-particle head word, one 64-bit value so that a reader always sees a consistent snapshot:
+//   bits 63..45  stamp = 1 + round of the last advance (0 = not advanced yet)
+//   bits 44..32  pos   = index in the sub-list of the current head entry (<= 8191)
+//   bit  31      LIVE  = the sub-list has a current head entry (0: empty, finished, or blocked in a slab's phase A)
+//   bit  30      OVF   = the sub-list is longer than 1 + LIST_CHUNK entries (chunk word 7 is a pool index)
+//   bits 29..0   the current head entry itself (partner, role, LAST)
+// Whether a pair is ready is decided from the two head words alone; the thread that runs the pair fetches each particle's
+// next entry from that particle's chunk (one 32-byte sector per particle, the same one every time).
+constexpr int HEAD_POS_BITS = 13;
+constexpr uint32_t HEAD_REM_MAX = (1u << HEAD_POS_BITS) - 1;            // longest sub-list
+constexpr uint32_t HEAD_STAMP_MAX = (1u << (32 - HEAD_POS_BITS)) - 1;
+constexpr uint32_t HEAD_LIVE = 1u << 31, HEAD_OVF = 1u << 30;
+__host__ __device__ __forceinline__ unsigned long long head_word(uint32_t stamp, uint32_t pos, uint32_t low) {
+    return ((unsigned long long)stamp << (32 + HEAD_POS_BITS)) | ((unsigned long long)pos << 32) | low;
 }
-__device__ __forceinline__ uint32_t head_stamp(unsigned long long h) { return (uint32_t)(h >> (32 + HEAD_REM_BITS)); }
-__device__ __forceinline__ uint32_t head_rem(unsigned long long h) { return (uint32_t)(h >> 32) & HEAD_REM_MAX; }
-__device__ __forceinline__ uint32_t head_entry(unsigned long long h) { return (uint32_t)h & ENT_MASK; }
-__device__ __forceinline__ PState ld_state(const PState* p) {
-    const uint4 v = *reinterpret_cast<const uint4*>(p);
-    return PState{(unsigned long long)v.x | ((unsigned long long)v.y << 32), v.z, v.w};
-}
-__device__ __forceinline__ PState ld_state_cg(const PState* p) {
-    const uint4 v = __ldcg(reinterpret_cast<const uint4*>(p));
-    return PState{(unsigned long long)v.x | ((unsigned long long)v.y << 32), v.z, v.w};
-}
-__device__ __forceinline__ void st_state(PState* p, unsigned long long head, uint32_t cursor, uint32_t next) {
-    *reinterpret_cast<uint4*>(p) = make_uint4((uint32_t)head, (uint32_t)(head >> 32), cursor, next);
+__device__ __forceinline__ uint32_t head_stamp(unsigned long long h) { return (uint32_t)(h >> (32 + HEAD_POS_BITS)); }
+__device__ __forceinline__ uint32_t head_pos(unsigned long long h) { return (uint32_t)(h >> 32) & HEAD_REM_MAX; }
+__device__ __forceinline__ uint32_t head_low(unsigned long long h) { return (uint32_t)h; }
+// entry j >= 1 of slot a's sub-list
+__device__ __forceinline__ uint32_t load_entry(const uint32_t* __restrict__ chunks, const uint32_t* __restrict__ pool, uint32_t a,
+                                               uint32_t j, uint32_t ovf) {
+    const uint32_t idx = j - 1u;
+    const uint32_t* c = chunks + (size_t)a * LIST_CHUNK;
+    if (!ovf || idx < LIST_CHUNK - 1u) return c[idx];
+    return pool[c[LIST_CHUNK - 1u] + (idx - (LIST_CHUNK - 1u))];
 }
 
-// One kernel builds every particle's contact sub-list.  Each candidate of the 3x3 block is tested
-// ONCE (three flat loops over the contiguous slot ranges of the left, own and right column) and the
-// hits are kept as a 64-bit mask; after a CTA-wide scan and one atomic per CTA that reserves the
-// CTA's range of `entries`, the mask is replayed in the reference's list order without touching
-// memory again.  A particle with more than 64 candidates takes the generic two-walk path.
-// Also seeds the first work list with {slot, first entry}.
+// detect_kernel builds every particle's contact sub-list.  A warp owns a span of consecutive slots and works alone
+// (no CTA barrier, no CTA-wide scan):
+//   phase 1  every slot of the span, 32 at a time: cell, the 3x3 block's slot ranges, every candidate tested ONCE in
+//            one flat loop over the three columns' ranges; slots with at least one hit (about a third of them at the
+//            reference density) are queued in shared memory as {slot, hit mask}
+//   phase 2  the queue, 32 at a time, so every lane has work: the hit mask is permuted into the reference's list order,
+//            entry 0 goes into the head word, the others into the slot's own chunk (nothing is reserved or scanned);
+//            particles that go on the first work list are compacted in place in the queue
+//   finally  one atomic reserves the span's piece of the first work list, written as one coalesced run.
+// A particle whose 3x3 block holds more than 32 candidates takes a generic two-walk path.
 //
 // Multi-GPU slabs (SLAB = true, ps_slab.cuh): the local grid has one ghost column on each side that
 // has a neighbour rank.  An entry is listed on this rank only if its CENTRE particle sits in an own
 // column (the pair list is ordered by centre, so a pair belongs to the rank that owns its centre);
 // particles of the first two local columns start "blocked" (their sub-list becomes visible only after
-// the left rank has handed over their state): their count goes to `brem`, their cursor word says 0 left.
+// the left rank has handed over their state): their head word is written without LIVE and `brem` is set.
 struct SlabView {
     uint32_t gl, gr;          // 1 if a left / right ghost column exists
     uint32_t ncl;             // local columns (own + ghosts)
@@ -392,93 +397,7 @@ struct SlabView {
     uint32_t* brem;           // per slot: sub-list length of a blocked particle
 };
 
-// Bit-mask helpers for the candidate masks: 32-bit when the 3x3 block holds at most 32 candidates (the usual case:
-// ~4 at the reference density), 64-bit up to 64, the generic two-walk path beyond.
-template <class M> struct MaskBits;
-template <> struct MaskBits<uint32_t> {
-    static constexpr uint32_t W = 32;
-    static __device__ __forceinline__ uint32_t range(uint32_t m, uint32_t off, uint32_t len) { return len ? ((m >> off) & (len >= 32u ? ~0u : ((1u << len) - 1u))) : 0u; }
-    static __device__ __forceinline__ uint32_t popc(uint32_t m) { return (uint32_t)__popc(m); }
-    static __device__ __forceinline__ uint32_t first(uint32_t m) { return (uint32_t)__ffs((int)m) - 1u; }
-    static __device__ __forceinline__ uint32_t one(uint32_t bit) { return 1u << bit; }
-};
-template <> struct MaskBits<unsigned long long> {
-    static constexpr uint32_t W = 64;
-    static __device__ __forceinline__ unsigned long long range(unsigned long long m, uint32_t off, uint32_t len) { return len ? ((m >> off) & (len >= 64u ? ~0ull : ((1ull << len) - 1ull))) : 0ull; }
-    static __device__ __forceinline__ uint32_t popc(unsigned long long m) { return (uint32_t)__popcll(m); }
-    static __device__ __forceinline__ uint32_t first(unsigned long long m) { return (uint32_t)__ffsll((long long)m) - 1u; }
-    static __device__ __forceinline__ unsigned long long one(uint32_t bit) { return 1ull << bit; }
-};
-
 struct OwnFlags { bool a_own, l_own, r_own; };   // which columns of the 3x3 block belong to this rank (all true on one GPU)
-
-// checkCollision (:339-346) for every candidate of the three column ranges, once: (xj-xi)^2 does not depend on which
-// of the two is i, so one test serves both roles.  Bit offset of slot q: left column q - l0, own column nL + q - m0,
-// right column nL + nM + q - r0.
-template <class Real, class M>
-__device__ __forceinline__ M test_block(const Rec<Real>* __restrict__ rec, uint32_t a, decltype(ld_pos((const Rec<Real>*)nullptr)) pa,
-                                        const Stencil& st, Real r2sq) {
-    M mask = 0;
-    uint32_t bit = 0;
-    auto test = [&](uint32_t b, uint32_t e) {
-        for (uint32_t q = b; q < e; ++q, ++bit) {
-            const auto pq = ld_pos(rec + q);
-            const Real dx = pq.x - pa.x, dy = pq.y - pa.y;
-            const Real d2 = dx * dx + dy * dy;
-            if (d2 < r2sq && q != a) mask |= MaskBits<M>::one(bit);
-        }
-    };
-    if (st.left) test(st.l0, st.l3);
-    test(st.m0, st.m3);
-    if (st.right) test(st.r0, st.r3);
-    return mask;
-}
-
-// number of entries in a's sub-list; own-cell partners appear twice (a as neighbour and a as centre, Q1)
-template <class M, bool SLAB>
-__device__ __forceinline__ uint32_t count_block(M mask, const Stencil& st, uint32_t nL, uint32_t nM, OwnFlags f) {
-    using B = MaskBits<M>;
-    if (!SLAB || (f.a_own && f.l_own && f.r_own))            // every column of the block is an own column: nothing to filter
-        return B::popc(mask) + B::popc(B::range(mask, nL + (st.m1 - st.m0), st.m2 - st.m1));
-    uint32_t cnt = 0;
-    if (f.l_own) cnt += B::popc(B::range(mask, 0u, st.l2 - st.l0));                        // a neighbour of left-column centres
-    if (f.r_own) cnt += B::popc(B::range(mask, nL + nM, st.r1 - st.r0));                   // ... of right-column centres
-    if (f.a_own) cnt += B::popc(B::range(mask, nL, nM))                                    // own column, both roles
-                      + B::popc(B::range(mask, nL + (st.m1 - st.m0), st.m2 - st.m1))       // own cell listed twice
-                      + B::popc(B::range(mask, nL + nM + (st.r1 - st.r0), st.r3 - st.r1))  // a centre, right column
-                      + B::popc(B::range(mask, st.l2 - st.l0, st.l3 - st.l2));             // a centre, (-1,1)
-    return cnt;
-}
-
-// replay the mask in the reference's list order (the eleven segments documented at walk_contacts)
-template <class M>
-__device__ __forceinline__ uint32_t emit_block(M mask, const Stencil& st, uint32_t a, uint32_t nL, uint32_t nM, OwnFlags f,
-                                               uint32_t* __restrict__ entries, uint32_t w) {
-    using B = MaskBits<M>;
-    auto emit = [&](uint32_t b, uint32_t e, uint32_t off, uint32_t o, uint32_t centre) {
-        if (e <= b) return;
-        M bits = B::range(mask, off, e - b);
-        while (bits) {
-            const uint32_t j = B::first(bits);
-            bits &= bits - 1;
-            entries[w++] = make_entry(b + j, o, centre);
-        }
-    };
-    const uint32_t oM = nL - st.m0, oR = nL + nM - st.r0;                // wrap-around arithmetic: offset = oX + q
-    if (st.left && f.l_own) { emit(st.l0, st.l1, 0u, 3u, 0u); emit(st.l1, st.l2, st.l1 - st.l0, 2u, 0u); }
-    if (f.a_own) {
-        emit(st.m0, st.m1, oM + st.m0, 1u, 0u);
-        emit(st.m1, a, oM + st.m1, 0u, 0u);
-        emit(st.m1, a, oM + st.m1, 0u, 1u);
-        emit(a + 1, st.m2, oM + a + 1, 0u, 1u);
-        emit(st.m2, st.m3, oM + st.m2, 1u, 1u);
-        if (st.right) { emit(st.r1, st.r2, oR + st.r1, 2u, 1u); emit(st.r2, st.r3, oR + st.r2, 3u, 1u); }
-        if (st.left) emit(st.l2, st.l3, st.l2 - st.l0, 4u, 1u);
-        emit(a + 1, st.m2, oM + a + 1, 0u, 0u);
-    }
-    if (st.right && f.r_own) emit(st.r0, st.r1, oR + st.r0, 4u, 0u);
-    return w;
-}
 
 #ifndef PS_DETECT_UNROLL
 #define PS_DETECT_UNROLL 2      // tuning knobs of detect_kernel.  Measured on B200 at 16 Mi particles, whole sub-step: unroll 1 / 4: +1.6 %;
@@ -549,135 +468,192 @@ __device__ __forceinline__ uint32_t list_mask(uint32_t hits, const Stencil& st, 
     return left | mid | right;
 }
 
-// Write the entries of a list-ordered mask; returns the first two (.x, .y; 0 where there is none).  Entry of list bit p
-// in run i = base_i + p with base_i = (first slot of the run - start of the run) + role bit, all modulo 2^32.
-__device__ __forceinline__ uint2 emit_list(uint32_t lm, const Stencil& st, uint32_t a, const ListRuns& r,
-                                           uint32_t* __restrict__ entries, uint32_t w) {
+// Where entry j >= 1 of a sub-list of `cnt` entries goes: the slot's chunk, or the overflow run at `run` in the pool.
+__device__ __forceinline__ void store_entry(uint32_t* __restrict__ chunk, uint32_t* __restrict__ pool, bool ovf, uint32_t run, uint32_t j, uint32_t e) {
+    const uint32_t idx = j - 1u;
+    if (!ovf || idx < LIST_CHUNK - 1u) chunk[idx] = e;
+    else pool[run + (idx - (LIST_CHUNK - 1u))] = e;
+}
+
+// Write the entries of a list-ordered mask (entry 0 is returned, for the head word; the last one carries ENT_LAST).
+// Entry of list bit p in run i = base_i + p with base_i = (first slot of the run - start of the run) + role bit, all
+// modulo 2^32.
+__device__ __forceinline__ uint32_t emit_list(uint32_t lm, const Stencil& st, uint32_t a, const ListRuns& r,
+                                              uint32_t* __restrict__ chunk, uint32_t* __restrict__ pool, bool ovf, uint32_t run) {
     const uint32_t b0 = st.l0, b1 = st.m0 - r.t1, b2 = st.m1 - r.t2 + ENT_CENTRE, b3 = a + 1u - r.t3 + ENT_CENTRE,
                    b4 = st.r1 - r.t4 + ENT_CENTRE, b5 = st.l2 - r.t5 + ENT_CENTRE, b6 = a + 1u - r.t6, b7 = st.r0 - r.t7;
-    uint2 head2 = make_uint2(0u, 0u);
-    uint32_t k = 0;
+    uint32_t e0 = 0u, j = 0u;
     while (lm) {
         const uint32_t p = (uint32_t)__ffs((int)lm) - 1u;
         lm &= lm - 1u;
         const uint32_t lo = p < r.t2 ? (p < r.t1 ? b0 : b1) : (p < r.t3 ? b2 : b3);
         const uint32_t hi = p < r.t6 ? (p < r.t5 ? b4 : b5) : (p < r.t7 ? b6 : b7);
-        const uint32_t e = (p < r.t4 ? lo : hi) + p;
-        entries[w++] = e;
-        if (k == 0) head2.x = e; else if (k == 1) head2.y = e;
-        ++k;
+        const uint32_t e = ((p < r.t4 ? lo : hi) + p) | (lm ? 0u : ENT_LAST);
+        if (j == 0u) e0 = e; else store_entry(chunk, pool, ovf, run, j, e);
+        ++j;
     }
-    return head2;
+    return e0;
+}
+
+constexpr uint32_t DETECT_SPAN_MAX = 256;   // slots per warp (a multiple of 32); the launch picks a shorter span for small scenes
+constexpr uint32_t DETECT_SLOW = 1u << 31;  // queue item flag: more than 32 candidates, take the generic walk
+
+// The cell of slot a's particle and the slot ranges of its 3x3 block (both phases need them; phase 2 recomputes them
+// for the third of the slots that got that far instead of carrying twelve words per slot through shared memory).
+template <class Real, bool SLAB>
+__device__ __forceinline__ Stencil locate(decltype(ld_pos((const Rec<Real>*)nullptr)) pa, const uint32_t* __restrict__ cell_start,
+                                          const StepConst<Real>& k, const SlabView& sv, DevState* __restrict__ ds, uint32_t a, uint32_t n,
+                                          OwnFlags& own) {
+    if (SLAB) {
+        // local cell: global computeCoordinate, then shift by the slab's first local column
+        const Real fi = floor_r(cell_coord<Real>(pa.x, k)), fj = floor_r(cell_coord<Real>(pa.y, k));
+        const uint32_t gi = fi > (Real)0 ? (fi < (Real)sv.gcols ? (uint32_t)fi : sv.gcols - 1) : 0u;
+        uint32_t gj = fj > (Real)0 ? (fj < (Real)k.rows ? (uint32_t)fj : k.rows - 1) : 0u;
+        uint32_t lx = gi - sv.col_off;
+        if (lx >= sv.ncl) {                                  // a record outside the local grid: corrupt state, stop before indexing with it
+            if (!atomicOr(&ds->flags, FLAG_CORRUPT)) { ds->dbg[0] = a; ds->dbg[1] = gi; ds->dbg[2] = gj; ds->dbg[3] = n; }
+            lx = 0; gj = 0;
+        }
+        own.a_own = lx >= sv.gl && lx < sv.ncl - sv.gr;
+        own.l_own = lx >= 1u && (lx - 1u) >= sv.gl && (lx - 1u) < sv.ncl - sv.gr;
+        own.r_own = (lx + 1u) >= sv.gl && (lx + 1u) < sv.ncl - sv.gr;
+        return load_stencil<Real>(cell_start, lx, gj, k.cols, k);
+    }
+    uint32_t gx, gy;
+    cell_xy<Real>(pa.x, pa.y, k, gx, gy);
+    return load_stencil<Real>(cell_start, gx, gy, k.cols, k);
+}
+
+// which of walk_contacts' entries this rank lists (all of them on one GPU)
+__device__ __forceinline__ bool keep_entry(bool slab, const OwnFlags& own, uint32_t o, uint32_t centre) {
+    return !slab || (centre ? own.a_own : (o >= 2u && o <= 3u ? own.l_own : (o == 4u ? own.r_own : own.a_own)));
 }
 
 template <class Real, bool SLAB>
-__global__ void __launch_bounds__(DETECT_THREADS, (sizeof(Real) == 4 ? PS_DETECT_MINB : 4) * 256 / DETECT_THREADS)   // 40 / 64 registers: more resident warps to hide the load latency
-detect_kernel(const Rec<Real>* __restrict__ rec, const uint32_t* __restrict__ cell_start, uint32_t n, StepConst<Real> k,
-              uint32_t* __restrict__ entries, uint32_t entries_cap, PState* __restrict__ state,
+__global__ void __launch_bounds__(DETECT_THREADS, (sizeof(Real) == 4 ? PS_DETECT_MINB : 4) * 256 / DETECT_THREADS)
+detect_kernel(const Rec<Real>* __restrict__ rec, const uint32_t* __restrict__ cell_start, uint32_t n, uint32_t span, StepConst<Real> k,
+              uint32_t* __restrict__ chunks, uint32_t* __restrict__ pool, uint32_t pool_cap, unsigned long long* __restrict__ head,
               uint2* __restrict__ wl0, DevState* __restrict__ ds, SlabView sv) {
-    __shared__ uint32_t sh_base, sh_wbase;
-    const uint32_t a = blockIdx.x * blockDim.x + threadIdx.x;
-    // SLAB: `n` is the record capacity on entry; the slot count lives on the device.  The slot's position is
-    // requested before that count is known (any slot below the capacity may be read), so the two loads overlap.
-    const auto pa = a < n ? ld_pos(rec + a) : decltype(ld_pos(rec)){};
-    if (SLAB) n = *sv.n_local;
-    // Error state: no lists, no resolve.  The flag can also be raised by another CTA of this launch, so threads of one CTA
-    // may disagree about it: nobody leaves before the CTA-wide scan and its barrier, dead threads just contribute nothing.
-    const bool dead = ds->flags != 0u;
-    const bool valid = a < n && !dead;
-    Stencil st{};
-    uint32_t cnt = 0, nL = 0, nM = 0;
-    uint32_t m32 = 0u;
-    unsigned long long m64 = 0ull;
-    int path = 0;                                            // 0: 32-bit mask, 1: 64-bit mask, 2: generic walk
-    OwnFlags own{true, true, true};
-    bool blocked = false, first_lower = false;
-    if (valid) {
-        if (SLAB) {
-            // local cell: global computeCoordinate, then shift by the slab's first local column
-            const Real fi = floor_r(cell_coord<Real>(pa.x, k)), fj = floor_r(cell_coord<Real>(pa.y, k));
-            const uint32_t gi = fi > (Real)0 ? (fi < (Real)sv.gcols ? (uint32_t)fi : sv.gcols - 1) : 0u;
-            uint32_t gj = fj > (Real)0 ? (fj < (Real)k.rows ? (uint32_t)fj : k.rows - 1) : 0u;
-            uint32_t lx = gi - sv.col_off;
-            if (lx >= sv.ncl) {                                  // a record outside the local grid: corrupt state, stop before indexing with it
-                if (!atomicOr(&ds->flags, FLAG_CORRUPT)) { ds->dbg[0] = a; ds->dbg[1] = gi; ds->dbg[2] = gj; ds->dbg[3] = n; }
-                lx = 0; gj = 0;
+    __shared__ uint2 queue[DETECT_THREADS / 32][DETECT_SPAN_MAX];     // per warp: {slot (+ DETECT_SLOW), hit mask}
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    const uint32_t below = (1u << lane) - 1u;
+    uint2* const q = queue[warp];
+    const uint32_t first = (blockIdx.x * (DETECT_THREADS / 32) + warp) * span;
+    uint32_t n_blocked = 0u;
+    if (SLAB) { n = *sv.n_local; n_blocked = *sv.n_blocked; }   // (`n` is the record capacity on entry; the slot count lives on the device)
+    if (first >= n) return;
+    // Error state (raised by an earlier launch, or by another warp of this one): no lists; the resolve kernel will not run.
+    if (__any_sync(0xffffffffu, ds->flags != 0u)) return;
+    const uint32_t end = first + span < n ? first + span : n;
+
+    // ---- phase 1: test every candidate once, queue the slots that hit something
+    uint32_t qn = 0u;                                        // queue length (same value in every lane)
+    for (uint32_t b0 = first; b0 < end; b0 += 32u) {
+        const uint32_t a = b0 + lane;
+        uint32_t hits = 0u, tag = a;
+        if (a < end) {
+            const auto pa = ld_pos(rec + a);
+            OwnFlags own{true, true, true};
+            const Stencil st = locate<Real, SLAB>(pa, cell_start, k, sv, ds, a, n, own);
+            const uint32_t nL = st.l3 - st.l0, nM = st.m3 - st.m0;     // (all zero when the column does not exist)
+            const uint32_t total = nL + nM + (st.r3 - st.r0);
+            // list length bound: every candidate once, own-cell partners twice
+            if (total + (st.m2 - st.m1) <= 32u) {
+                hits = test_flat<Real>(rec, a, pa, st, nL, nM, total, k.r2sq);
+            } else {
+                hits = 1u; tag = a | DETECT_SLOW;            // phase 2 walks the block itself
             }
-            own.a_own = lx >= sv.gl && lx < sv.ncl - sv.gr;
-            own.l_own = lx >= 1u && (lx - 1u) >= sv.gl && (lx - 1u) < sv.ncl - sv.gr;
-            own.r_own = (lx + 1u) >= sv.gl && (lx + 1u) < sv.ncl - sv.gr;
-            blocked = a < *sv.n_blocked;
-            st = load_stencil<Real>(cell_start, lx, gj, k.cols, k);
-        } else {
-            uint32_t gx, gy;
-            cell_xy<Real>(pa.x, pa.y, k, gx, gy);
-            st = load_stencil<Real>(cell_start, gx, gy, k.cols, k);
+            if (SLAB) head[a] = 0ull;                        // slab_right_check_kernel looks at every slot of the last two columns
         }
-        nL = st.l3 - st.l0;                                   // (all zero when the column does not exist)
-        nM = st.m3 - st.m0;
-        const uint32_t total = nL + nM + (st.r3 - st.r0);
-        // list length bound: every candidate once, own-cell partners twice
-        path = total + (st.m2 - st.m1) <= 32u ? 0 : (total <= 64u ? 1 : 2);
-        if (path == 0) {
-            const uint32_t hits = test_flat<Real>(rec, a, pa, st, nL, nM, total, k.r2sq);
-            const ListRuns lr = list_runs(st, a);
-            m32 = list_mask(hits, st, a, nL, nM, lr, own);
-            cnt = (uint32_t)__popc(m32);
-            // Round 0 runs a ready pair from its lower slot (resolve_item), so a particle whose first partner has a
-            // lower slot has nothing to do there: it stays off the first work list.  Runs 3, 4, 6, 7 hold the higher slots.
-            if (m32) {
-                const uint32_t p = (uint32_t)__ffs((int)m32) - 1u;
-                first_lower = !((p >= lr.t3 && p < lr.t5) || p >= lr.t6);
+        const uint32_t push = __ballot_sync(0xffffffffu, hits != 0u);
+        if (hits) q[qn + (uint32_t)__popc(push & below)] = make_uint2(tag, hits);
+        qn += (uint32_t)__popc(push);
+    }
+    __syncwarp();
+
+    // ---- phase 2: the queued slots, full warps
+    uint32_t wn = 0u;                                        // particles kept for the first work list, compacted at the front of the queue
+    uint32_t my_entries = 0u;                                // statistics: entries written by this lane
+    for (uint32_t i0 = 0; i0 < qn; i0 += 32u) {
+        const bool live = i0 + lane < qn;
+        const uint2 it = live ? q[i0 + lane] : make_uint2(0u, 0u);
+        __syncwarp();                                        // everything of this batch is read before the compaction below writes
+        const uint32_t a = it.x & ~DETECT_SLOW;
+        bool listed = false;
+        uint32_t e0 = 0u;
+        if (live) {
+            const auto pa = ld_pos(rec + a);
+            OwnFlags own{true, true, true};
+            const Stencil st = locate<Real, SLAB>(pa, cell_start, k, sv, ds, a, n, own);
+            const bool blocked = SLAB && a < n_blocked;
+            uint32_t* chunk = chunks + (size_t)a * LIST_CHUNK;
+            uint32_t cnt = 0u, run = 0u;
+            bool first_lower = false, fits = true;
+            if (!(it.x & DETECT_SLOW)) {
+                const uint32_t nL = st.l3 - st.l0, nM = st.m3 - st.m0;
+                const ListRuns lr = list_runs(st, a);
+                const uint32_t m32 = list_mask(it.y, st, a, nL, nM, lr, own);
+                cnt = (uint32_t)__popc(m32);
+                const bool ovf = cnt > LIST_CHUNK + 1u;
+                if (ovf) {                                   // rare: a run in the pool for entries 8.. (one atomic per such particle)
+                    run = atomicAdd(&ds->pool_used, cnt - LIST_CHUNK);
+                    fits = (uint64_t)run + (cnt - LIST_CHUNK) <= pool_cap;
+                    if (fits) chunk[LIST_CHUNK - 1u] = run;
+                }
+                if (cnt && fits) {
+                    // Round 0 runs a ready pair from its lower slot (resolve_item), so a particle whose first partner has a
+                    // lower slot has nothing to do there: it stays off the first work list.  Runs 3, 4, 6, 7 hold the higher slots.
+                    const uint32_t p = (uint32_t)__ffs((int)m32) - 1u;
+                    first_lower = !((p >= lr.t3 && p < lr.t5) || p >= lr.t6);
+                    e0 = emit_list(m32, st, a, lr, chunk, pool, ovf, run) | (ovf ? HEAD_OVF : 0u);
+                }
+            } else {
+                walk_contacts<Real>(a, rec, st, k.r2sq, [&](uint32_t, uint32_t o, uint32_t centre) { cnt += keep_entry(SLAB, own, o, centre) ? 1u : 0u; });
+                const bool ovf = cnt > LIST_CHUNK + 1u;
+                fits = cnt <= HEAD_REM_MAX;
+                if (!fits) atomicOr(&ds->flags, FLAG_LIST_TOO_LONG);
+                if (ovf && fits) {
+                    run = atomicAdd(&ds->pool_used, cnt - LIST_CHUNK);
+                    fits = (uint64_t)run + (cnt - LIST_CHUNK) <= pool_cap;
+                    if (fits) chunk[LIST_CHUNK - 1u] = run;
+                }
+                if (cnt && fits) {
+                    uint32_t j = 0u;
+                    walk_contacts<Real>(a, rec, st, k.r2sq, [&](uint32_t qq, uint32_t o, uint32_t centre) {
+                        if (!keep_entry(SLAB, own, o, centre)) return;
+                        const uint32_t e = make_entry(qq, o, centre) | (j + 1u == cnt ? ENT_LAST : 0u);
+                        if (j == 0u) { e0 = e; first_lower = qq < a; } else store_entry(chunk, pool, ovf, run, j, e);
+                        ++j;
+                    });
+                    if (ovf) e0 |= HEAD_OVF;
+                }
             }
-        } else if (path == 1) {
-            m64 = test_block<Real, unsigned long long>(rec, a, pa, st, k.r2sq);
-            cnt = count_block<unsigned long long, SLAB>(m64, st, nL, nM, own);
-        } else {
-            walk_contacts<Real>(a, rec, st, k.r2sq, [&](uint32_t, uint32_t o, uint32_t centre) {
-                const bool keep = !SLAB || (centre ? own.a_own : (o >= 2u && o <= 3u ? own.l_own : (o == 4u ? own.r_own : own.a_own)));
-                cnt += keep ? 1u : 0u;
-            });
+            if (!fits) {                                     // does not fit: flag; the resolve kernel will not run
+                atomicOr(&ds->flags, FLAG_CAPACITY);
+                head[a] = 0ull;
+            } else if (cnt) {
+                head[a] = head_word(0u, 0u, e0 | (blocked ? 0u : HEAD_LIVE));
+                if (SLAB && blocked) sv.brem[a] = cnt;       // brem is zero everywhere else (cleared at creation and by the unblock kernel)
+                listed = !blocked && !first_lower;
+                my_entries += cnt;
+            } else if (!SLAB) {
+                head[a] = 0ull;                              // (hits only with particles whose pair another rank lists: SLAB wrote 0 above)
+            }
         }
+        const uint32_t lb = __ballot_sync(0xffffffffu, listed);
+        if (listed) q[wn + (uint32_t)__popc(lb & below)] = make_uint2(a, e0);
+        wn += (uint32_t)__popc(lb);
     }
-    // packed CTA scan: entry count in the low 22 bits, "goes on the first work list" flag above
-    const bool listed = cnt && !blocked && !first_lower;
-    const uint32_t packed = cnt | ((listed ? 1u : 0u) << 22);
-    uint32_t total;
-    const uint32_t ex = block_exclusive_scan<DETECT_THREADS>(packed, &total);
-    if (threadIdx.x == 0) {
-        const uint32_t te = total & ((1u << 22) - 1), tw = total >> 22;
-        sh_base = te ? atomicAdd(&ds->entries_used, te) : 0u;
-        sh_wbase = tw ? atomicAdd(&ds->wl_count[0], tw) : 0u;
+    __syncwarp();
+    // ---- the span's piece of the first work list, and the entry count for the statistics
+    my_entries = __reduce_add_sync(0xffffffffu, my_entries);
+    uint32_t wbase = 0u;
+    if (lane == 0) {
+        if (my_entries) atomicAdd(&ds->entries_used, my_entries);
+        if (wn) wbase = atomicAdd(&ds->wl_count[0], wn);
     }
-    __syncthreads();
-    if (!valid) {
-        if (dead && a < n) st_state(state + a, 0ull, 0u, 0u);
-        return;
-    }
-    const uint32_t te = total & ((1u << 22) - 1);
-    const uint32_t begin = sh_base + (ex & ((1u << 22) - 1));
-    if ((uint64_t)sh_base + te > entries_cap || cnt > HEAD_REM_MAX) {   // does not fit: flag; the resolve kernel will not run
-        atomicOr(&ds->flags, cnt > HEAD_REM_MAX ? FLAG_LIST_TOO_LONG : FLAG_CAPACITY);
-        st_state(state + a, 0ull, 0u, 0u);
-        return;
-    }
-    if (SLAB && blocked) sv.brem[a] = cnt;                   // brem is zero everywhere else (cleared at creation and by the unblock kernel)
-    if (!cnt) { st_state(state + a, 0ull, begin, 0u); return; }
-    uint2 head2;
-    if (path == 0) {
-        head2 = emit_list(m32, st, a, list_runs(st, a), entries, begin);
-    } else if (path == 1) {
-        emit_block<unsigned long long>(m64, st, a, nL, nM, own, entries, begin);
-    } else {
-        uint32_t w = begin;
-        walk_contacts<Real>(a, rec, st, k.r2sq, [&](uint32_t q, uint32_t o, uint32_t centre) {
-            const bool keep = !SLAB || (centre ? own.a_own : (o >= 2u && o <= 3u ? own.l_own : (o == 4u ? own.r_own : own.a_own)));
-            if (keep) entries[w++] = make_entry(q, o, centre);
-        });
-    }
-    if (path != 0) head2 = make_uint2(entries[begin], cnt > 1u ? entries[begin + 1u] : 0u);
-    st_state(state + a, head_word(0u, blocked ? 0u : cnt, head2.x), begin, head2.y);
-    if (listed) wl0[sh_wbase + (ex >> 22)] = make_uint2(a, head2.x);
+    wbase = __shfl_sync(0xffffffffu, wbase, 0);
+    for (uint32_t i = lane; i < wn; i += 32u) wl0[wbase + i] = q[i];
 }
 
 
@@ -753,8 +729,8 @@ constexpr uint32_t RESOLVE_TAIL_CAP = 2 * RESOLVE_TAIL;   // a round appends at 
 // rounds keeps coherent with the CTA's own writes.  Chains revisit the same few particles round after round, so the
 // L1 hits cut the per-round latency.  (Nothing was loaded through L1 earlier in the kernel, so no stale lines exist.)
 template <class Real, bool LOCAL>
-__device__ __forceinline__ int resolve_item(Rec<Real>* rec, const uint32_t* __restrict__ entries, PState* state,
-                                            uint2 item, uint32_t r, const StepConst<Real>& k, uint2 (&next)[2]) {
+__device__ __forceinline__ int resolve_item(Rec<Real>* rec, const uint32_t* __restrict__ chunks, const uint32_t* __restrict__ pool,
+                                            unsigned long long* head, uint2 item, uint32_t r, const StepConst<Real>& k, uint2 (&next)[2]) {
     const uint32_t a = item.x, ea = item.y;
     const uint32_t b = ea & ENT_SLOT_MASK;
     // Round 0: every particle with a visible list is on the work list, and a pair can only be ready if the two
@@ -762,41 +738,41 @@ __device__ __forceinline__ int resolve_item(Rec<Real>* rec, const uint32_t* __re
     if (r == 0u && b < a) return 0;
     // everything that depends only on the item is requested at once (the records speculatively): one round trip to
     // memory decides whether the pair runs and brings what it needs
-    const PState sa = LOCAL ? ld_state(state + a) : ld_state_cg(state + a);
-    const PState sb = LOCAL ? ld_state(state + b) : ld_state_cg(state + b);
+    const unsigned long long ha = LOCAL ? head[a] : __ldcg(head + a);
+    const unsigned long long hb = LOCAL ? head[b] : __ldcg(head + b);
     const Rec<Real> Ra = LOCAL ? ld_rec(rec + a) : ld_rec_cg(rec + a), Rb = LOCAL ? ld_rec(rec + b) : ld_rec_cg(rec + b);
-    const unsigned long long ha = sa.head, hb = sb.head;
     if (head_stamp(ha) == r + 1) return 0;           // a already ran a pair this round (executed by its partner)
     if (head_stamp(hb) == r + 1) return 0;           // b moved this round; b is on the next list and will look at a
-    const uint32_t rem_a = head_rem(ha), rem_b = head_rem(hb);
-    if (rem_b == 0) return 0;                        // (rem_a > 0: a is on the list)
+    const uint32_t wa = head_low(ha), wb = head_low(hb);
+    if (!(wb & HEAD_LIVE)) return 0;                 // (a is live: it is on the list)
     // same pair seen from the other side: partner = a, opposite role
-    if (head_entry(hb) != (a | (~ea & ENT_CENTRE))) return 0;
+    if ((wb & ENT_SLOT_MASK) != a || !((wb ^ ea) & ENT_CENTRE)) return 0;
     // Both particles on this round's list (b's head last moved in round r-1, or never when r = 0): the
     // lower slot runs the pair.  Membership is read from the SAME 64-bit word as the head entry, so a
     // concurrent executor cannot make the two threads disagree.
     if (b < a && head_stamp(hb) == r) return 0;
-    // the entries that become `next` after the advance (requested now, needed only when the state is written back)
-    const uint32_t nn_a = rem_a > 2 ? entries[sa.cursor + 2] : 0u;
-    const uint32_t nn_b = rem_b > 2 ? entries[sb.cursor + 2] : 0u;
-    const bool a_centre = (ea >> ENT_ROLE_BIT) != 0; // entry = {particle_i = neighbour, particle_j = centre}
+    // the two particles' next entries (requested now, needed only when the head words are written back)
+    const uint32_t pos_a = head_pos(ha), pos_b = head_pos(hb);
+    const bool more_a = !(wa & ENT_LAST), more_b = !(wb & ENT_LAST);
+    const uint32_t na = more_a ? (load_entry(chunks, pool, a, pos_a + 1u, wa & HEAD_OVF) | HEAD_LIVE | (wa & HEAD_OVF)) : 0u;
+    const uint32_t nb = more_b ? (load_entry(chunks, pool, b, pos_b + 1u, wb & HEAD_OVF) | HEAD_LIVE | (wb & HEAD_OVF)) : 0u;
+    const bool a_centre = (ea >> ENT_ROLE_BIT) & 1u; // entry = {particle_i = neighbour, particle_j = centre}
     Rec<Real> I = a_centre ? Rb : Ra, J = a_centre ? Ra : Rb;
     resolve_pair<Real>(I, J, k);
     st_rec(rec + (a_centre ? b : a), I);
     st_rec(rec + (a_centre ? a : b), J);
-    st_state(state + a, head_word(r + 1, rem_a - 1, rem_a > 1 ? sa.next : 0u), sa.cursor + 1, nn_a);
-    st_state(state + b, head_word(r + 1, rem_b - 1, rem_b > 1 ? sb.next : 0u), sb.cursor + 1, nn_b);
-    const uint2 na = make_uint2(a, sa.next), nb = make_uint2(b, sb.next);
-    const bool more_a = rem_a > 1, more_b = rem_b > 1;     // (constant indices keep `next` in registers)
-    next[0] = more_a ? na : nb;
-    next[1] = nb;
+    head[a] = head_word(r + 1, pos_a + 1u, na);
+    head[b] = head_word(r + 1, pos_b + 1u, nb);
+    const uint2 ia = make_uint2(a, na), ib = make_uint2(b, nb);     // (constant indices keep `next` in registers)
+    next[0] = more_a ? ia : ib;
+    next[1] = ib;
     return (more_a ? 1 : 0) + (more_b ? 1 : 0);
 }
 
 // One round over the work list `wl[0..cnt)` by one or many CTAs; appends the particles advanced in this round, with
 // their new head entry, to `out` (buffered per CTA: one global atomic per batch of 256 items).
 template <class Real>
-__device__ __forceinline__ void resolve_round(Rec<Real>* rec, const uint32_t* __restrict__ entries, PState* state,
+__device__ __forceinline__ void resolve_round(Rec<Real>* rec, const uint32_t* __restrict__ chunks, const uint32_t* __restrict__ pool, unsigned long long* head,
                                               const uint2* wl, uint32_t cnt, uint2* out, uint32_t* out_count, uint32_t r,
                                               uint32_t first, uint32_t stride, uint32_t cta_threads, const StepConst<Real>& k,
                                               uint2* sh_buf, uint32_t* sh_cnt, uint32_t* sh_base) {
@@ -806,7 +782,7 @@ __device__ __forceinline__ void resolve_round(Rec<Real>* rec, const uint32_t* __
         const uint32_t idx = base + threadIdx.x;
         if (idx < cnt) {
             uint2 next[2];
-            const int m = resolve_item<Real, false>(rec, entries, state, __ldcg(wl + idx), r, k, next);
+            const int m = resolve_item<Real, false>(rec, chunks, pool, head, __ldcg(wl + idx), r, k, next);
             for (int i = 0; i < m; ++i) sh_buf[atomicAdd(sh_cnt, 1u)] = next[i];
         }
         __syncthreads();
@@ -826,7 +802,7 @@ __device__ __forceinline__ void resolve_round(Rec<Real>* rec, const uint32_t* __
 // the chain of dependent L2 round trips of one batch overlaps with those of the other warps' batches.
 constexpr uint32_t RESOLVE_WBUF = 128;   // items per warp buffer; a batch appends at most 64
 template <class Real>
-__device__ __forceinline__ void resolve_round_warps(Rec<Real>* rec, const uint32_t* __restrict__ entries, PState* state,
+__device__ __forceinline__ void resolve_round_warps(Rec<Real>* rec, const uint32_t* __restrict__ chunks, const uint32_t* __restrict__ pool, unsigned long long* head,
                                                     const uint2* wl, uint32_t cnt, uint2* out, uint32_t* out_count, uint32_t r,
                                                     uint32_t first, uint32_t stride, const StepConst<Real>& k, uint2* sh_wbuf) {
     const uint32_t lane = threadIdx.x & 31u;
@@ -849,7 +825,7 @@ __device__ __forceinline__ void resolve_round_warps(Rec<Real>* rec, const uint32
         const uint32_t ahead = idx + stride;
         if (ahead < cnt) item = __ldcg(wl + ahead);
         uint2 next[2];
-        const int m = live ? resolve_item<Real, false>(rec, entries, state, cur, r, k, next) : 0;
+        const int m = live ? resolve_item<Real, false>(rec, chunks, pool, head, cur, r, k, next) : 0;
         const uint32_t one = __ballot_sync(0xffffffffu, m >= 1), two = __ballot_sync(0xffffffffu, m >= 2);
         if (one) {
             const uint32_t below = (1u << lane) - 1u;
@@ -865,7 +841,7 @@ __device__ __forceinline__ void resolve_round_warps(Rec<Real>* rec, const uint32
 
 template <class Real>
 __global__ void __launch_bounds__(RESOLVE_THREADS)
-resolve_kernel(Rec<Real>* rec, const uint32_t* __restrict__ entries, PState* state,
+resolve_kernel(Rec<Real>* rec, const uint32_t* __restrict__ chunks, const uint32_t* __restrict__ pool, unsigned long long* head,
                uint2* wl0, uint2* wl1, uint2* wl2, StepConst<Real> k, DevState* ds, uint32_t r_start) {
     cg::grid_group grid = cg::this_grid();
     __shared__ uint2 sh_buf[(RESOLVE_THREADS / 32) * RESOLVE_WBUF];   // grid phase: one append buffer per warp; tail: one for the CTA
@@ -886,7 +862,7 @@ resolve_kernel(Rec<Real>* rec, const uint32_t* __restrict__ entries, PState* sta
         if (trace && r < 64) { ds->trace_cnt[r] = cnt; ds->trace_ns[r] = (uint32_t)(global_ns() - t_begin); }
         if (cnt <= RESOLVE_TAIL) break;                      // same value in every thread: the whole grid leaves together
         if (leader) ds->wl_count[nn] = 0;                    // consumed in round r-1, refilled in round r+1
-        resolve_round_warps<Real>(rec, entries, state, list(cur), cnt, list(nxt), &ds->wl_count[nxt], r,
+        resolve_round_warps<Real>(rec, chunks, pool, head, list(cur), cnt, list(nxt), &ds->wl_count[nxt], r,
                                   blockIdx.x * RESOLVE_THREADS, gridDim.x * RESOLVE_THREADS, k, sh_buf);
         grid.sync();
     }
@@ -916,7 +892,7 @@ resolve_kernel(Rec<Real>* rec, const uint32_t* __restrict__ entries, PState* sta
                 continue;
             }
             if (threadIdx.x == 0) ds->wl_count[nn] = 0;
-            resolve_round<Real>(rec, entries, state, list(cur), cnt, list(nxt), &ds->wl_count[nxt], r,
+            resolve_round<Real>(rec, chunks, pool, head, list(cur), cnt, list(nxt), &ds->wl_count[nxt], r,
                                 0u, RESOLVE_TAIL_THREADS, RESOLVE_TAIL_THREADS, k, sh_buf, &sh_cnt, &sh_base);
             __threadfence();
             __syncthreads();
@@ -940,7 +916,7 @@ resolve_kernel(Rec<Real>* rec, const uint32_t* __restrict__ entries, PState* sta
         uint2* out = tl_items + nxt * RESOLVE_TAIL_CAP;
         for (uint32_t idx = threadIdx.x; idx - lane < cnt; idx += RESOLVE_TAIL_THREADS) {   // whole warps: the ballots below need every lane
             uint2 next[2];
-            const int m = idx < cnt ? resolve_item<Real, true>(rec, entries, state, in[idx], r, k, next) : 0;
+            const int m = idx < cnt ? resolve_item<Real, true>(rec, chunks, pool, head, in[idx], r, k, next) : 0;
             const uint32_t one = __ballot_sync(0xffffffffu, m >= 1), two = __ballot_sync(0xffffffffu, m >= 2);
             if (one) {
                 uint32_t base = 0;
@@ -972,6 +948,19 @@ resolve_kernel(Rec<Real>* rec, const uint32_t* __restrict__ entries, PState* sta
 
 
 // ---- host side ---------------------------------------------------------------------------------
+// slots per detect warp: 256 for large scenes (few atomics, long coalesced work-list runs), shorter when that would
+// leave SMs without work
+inline uint32_t detect_span(uint64_t n) {
+    uint64_t batches = n / (32ull * 148 * 48);
+    if (batches < 1) batches = 1;
+    if (batches > DETECT_SPAN_MAX / 32) batches = DETECT_SPAN_MAX / 32;
+    return (uint32_t)batches * 32u;
+}
+inline unsigned detect_grid(uint64_t n, uint32_t span) {
+    const uint64_t warps = (n + span - 1) / span;
+    return (unsigned)((warps + DETECT_THREADS / 32 - 1) / (DETECT_THREADS / 32));
+}
+
 template <class Real>
 struct Collider {
     uint64_t n = 0;
@@ -988,8 +977,9 @@ struct Collider {
     Rec<Real>* rec[2] = {nullptr, nullptr};
     uint32_t* pid[2] = {nullptr, nullptr};
     uint32_t *ctr_count = nullptr, *ctr_off = nullptr;
-    uint32_t* entries = nullptr; uint32_t entries_cap = 0;
-    PState* state = nullptr;
+    uint32_t* chunks = nullptr;                              // LIST_CHUNK entry words per slot
+    uint32_t* entries = nullptr; uint32_t entries_cap = 0;   // overflow pool of the contact lists
+    unsigned long long* head = nullptr;
     uint2* wl[3] = {nullptr, nullptr, nullptr};
     uint64_t* pairs = nullptr; uint32_t pairs_cap = 0;
     DevState* ds = nullptr;
@@ -1019,7 +1009,8 @@ struct Collider {
             if ((rc = alloc(&pid[i], n, err))) return rc;
         }
         if ((rc = alloc(&entries, (uint64_t)entries_cap, err))) return rc;
-        if ((rc = alloc(&state, n, err))) return rc;
+        if ((rc = alloc(&head, n, err))) return rc;
+        if ((rc = alloc(&chunks, (uint64_t)LIST_CHUNK * n, err))) return rc;
         for (int i = 0; i < 3; ++i) if ((rc = alloc(&wl[i], n, err))) return rc;
         if ((rc = alloc(&ds, 1, err))) return rc;
         PS_CUDA_TRY(err, cudaMemsetAsync(ds, 0, sizeof(DevState), st));
@@ -1036,7 +1027,7 @@ struct Collider {
 
     void destroy() {
         cudaFree(cell_count); cudaFree(cell_start); cudaFree(scan_sums); cudaFree(slot_cell); cudaFree(arrival);
-        cudaFree(tmp_id); cudaFree(ctr_count); cudaFree(ctr_off); cudaFree(entries); cudaFree(state);
+        cudaFree(tmp_id); cudaFree(ctr_count); cudaFree(ctr_off); cudaFree(entries); cudaFree(head); cudaFree(chunks);
         for (auto& r : rec) cudaFree(r);
         for (auto& p : pid) cudaFree(p);
         for (auto& w : wl) cudaFree(w);
@@ -1056,6 +1047,8 @@ struct Collider {
 
     // The caller wrote new SoA arrays (upload): the records are stale.
     void invalidate_records() { rec_valid = false; soa_valid = true; }
+    // ... and whatever stopped the previous scene (capacity, cell overflow) no longer applies
+    cudaError_t clear_flags(cudaStream_t st) { return cudaMemsetAsync(&ds->flags, 0, sizeof(uint32_t), st); }
 
     // Bring the SoA arrays (original index order) up to date with the records.
     int materialize_soa(Real* px, Real* py, Real* vx, Real* vy, cudaStream_t st, Error& err, uint64_t* launches) {
@@ -1086,7 +1079,10 @@ struct Collider {
         PS_CUDA_TRY(err, exclusive_scan<uint8_t>(reinterpret_cast<const uint8_t*>(cell_count), cell_start, ncell, scan_sums, cell_start + ncell, &ds->max_cell, st));
         place_kernel<<<(gn + SORT_ILP - 1) / SORT_ILP, 256, 0, st>>>(slot_cell, arrival, pid[cur], cell_start, n32, tmp_id);
         move_kernel<Real><<<(gn + SORT_ILP - 1) / SORT_ILP, 256, 0, st>>>(rec[cur], pid[cur], slot_cell, cell_start, tmp_id, n32, k, rec[nw], pid[nw], ds);
-        detect_kernel<Real, false><<<(unsigned)((n + DETECT_THREADS - 1) / DETECT_THREADS), DETECT_THREADS, 0, st>>>(rec[nw], cell_start, n32, k, entries, entries_cap, state, wl[0], ds, SlabView{});
+        {
+            const uint32_t span = detect_span(n);
+            detect_kernel<Real, false><<<detect_grid(n, span), DETECT_THREADS, 0, st>>>(rec[nw], cell_start, n32, span, k, chunks, entries, entries_cap, head, wl[0], ds, SlabView{});
+        }
         *launches += 7;
         if (capture) {
             count_centre_kernel<Real><<<gn, 256, 0, st>>>(rec[nw], cell_start, n32, k, ctr_count);
@@ -1095,10 +1091,10 @@ struct Collider {
             *launches += 5;
         }
         {
-            Rec<Real>* a_rec = rec[nw]; const uint32_t* a_ent = entries;
-            PState* a_head = state; uint2 *a0 = wl[0], *a1 = wl[1], *a2 = wl[2];
+            Rec<Real>* a_rec = rec[nw]; const uint32_t* a_chunks = chunks; const uint32_t* a_ent = entries;
+            unsigned long long* a_head = head; uint2 *a0 = wl[0], *a1 = wl[1], *a2 = wl[2];
             StepConst<Real> a_k = k; DevState* a_ds = ds; uint32_t a_r0 = 0;
-            void* args[] = {&a_rec, &a_ent, &a_head, &a0, &a1, &a2, &a_k, &a_ds, &a_r0};
+            void* args[] = {&a_rec, &a_chunks, &a_ent, &a_head, &a0, &a1, &a2, &a_k, &a_ds, &a_r0};
             const uint64_t want = (n + RESOLVE_THREADS - 1) / RESOLVE_THREADS;
             const unsigned grid = (unsigned)(want < (uint64_t)resolve_grid ? want : (uint64_t)resolve_grid);
             PS_CUDA_TRY(err, cudaLaunchCooperativeKernel((const void*)resolve_kernel<Real>, dim3(grid), dim3(RESOLVE_THREADS), args, 0, st));
@@ -1120,7 +1116,7 @@ struct Collider {
         }
         if (h.flags & FLAG_CAPACITY) {
             err.status = PS_ERR_CAPACITY;
-            err.text = "contact list exceeded its capacity (" + std::to_string(entries_cap) + " entries); raise ps_config.contacts_per_particle";
+            err.text = "the overflow pool of the contact lists (" + std::to_string(entries_cap) + " entries, for particles with more than 9 contacts) is full; raise ps_config.contacts_per_particle";
             return err.status;
         }
         if (h.flags & FLAG_CELL_OVERFLOW) {

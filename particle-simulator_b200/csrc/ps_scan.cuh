@@ -1,6 +1,7 @@
-// ps_scan.cuh — exclusive prefix sum over uint32 arrays (computeStartArray, src/core.zig:137-142,
-// and the per-particle contact-list offsets).  Three launches: per-tile reduce, a one-block scan
-// of the tile sums, per-tile scan + offset.  12 B of HBM traffic per element.
+// ps_scan.cuh — exclusive prefix sum over u8 or u32 items (computeStartArray, src/core.zig:137-142, over the u8 cell
+// counters; the pair-capture offsets over u32).  Three launches: per-tile reduce, a one-block scan of the tile sums,
+// per-tile scan + offset.  HBM traffic per element: the input read twice, a u32 written = 6 B for the u8 counters,
+// 12 B for u32 items.
 #pragma once
 #include "ps_common.cuh"
 

@@ -154,6 +154,7 @@ slab_begin_kernel(SlabDev* __restrict__ sd, DevState* __restrict__ ds, void* sen
         sd->own_b_prev = sd->own_b;
         sd->right_incomplete = 0;
         ds->entries_used = 0;
+        ds->pool_used = 0;
         reinterpret_cast<HaloHeader*>(send_l)->count = 0;
         reinterpret_cast<HaloHeader*>(send_r)->count = 0;
     }
@@ -332,23 +333,22 @@ slab_move_kernel(const Rec<Real>* __restrict__ rec_old, const uint32_t* __restri
 
 // after phase A: do the particles of the last two local columns still have pending pairs?
 __global__ void __launch_bounds__(256)
-slab_right_check_kernel(const PState* __restrict__ state, const uint32_t* __restrict__ brem, SlabDev* __restrict__ sd) {
+slab_right_check_kernel(const unsigned long long* __restrict__ head, const uint32_t* __restrict__ brem, SlabDev* __restrict__ sd) {
     const uint32_t a = sd->c_last2 + blockIdx.x * blockDim.x + threadIdx.x;
     if (a >= sd->n_local) return;
-    if (head_rem(state[a].head) != 0u || brem[a] != 0u) sd->right_incomplete = 1u;
+    if ((head_low(head[a]) & HEAD_LIVE) || brem[a] != 0u) sd->right_incomplete = 1u;
 }
 
 // M1 has been received into the records of the first two local columns: make their sub-lists visible
 __global__ void __launch_bounds__(256)
-slab_unblock_kernel(PState* __restrict__ state, uint32_t* __restrict__ brem, uint2* __restrict__ wl, uint32_t* __restrict__ wl_count,
+slab_unblock_kernel(unsigned long long* __restrict__ head, uint32_t* __restrict__ brem, uint2* __restrict__ wl, uint32_t* __restrict__ wl_count,
                     uint32_t r0, const SlabDev* __restrict__ sd) {
     const uint32_t a = blockIdx.x * blockDim.x + threadIdx.x;
     if (a >= sd->n_blocked) return;
-    const uint32_t rem = brem[a];
-    if (!rem) return;
+    if (!brem[a]) return;
     brem[a] = 0u;
-    const uint32_t e = head_entry(state[a].head);               // written by detect; cursor and next are already in place
-    state[a].head = head_word(r0, rem, e);                      // stamp r0 = "on the work list of round r0"
+    const uint32_t e = head_low(head[a]) | HEAD_LIVE;            // entry 0 as detect left it, now visible
+    head[a] = head_word(r0, 0u, e);                              // stamp r0 = "on the work list of round r0"
     wl[atomicAdd(wl_count, 1u)] = make_uint2(a, e);
 }
 
@@ -409,8 +409,9 @@ struct SlabCollider {
     uint32_t* pid[2] = {nullptr, nullptr};
     uint32_t *cell_count = nullptr, *cell_start = nullptr, *scan_sums = nullptr;
     uint32_t *slot_cell = nullptr, *arrival = nullptr, *tmp_id = nullptr, *brem = nullptr;
+    uint32_t* chunks = nullptr;
     uint32_t* entries = nullptr; uint32_t entries_cap = 0;
-    PState* state = nullptr;
+    unsigned long long* head = nullptr;
     uint2* wl[3] = {nullptr, nullptr, nullptr};
     void *send_l = nullptr, *send_r = nullptr, *recv_l = nullptr, *recv_r = nullptr;
     DevState* ds = nullptr;
@@ -517,7 +518,9 @@ struct SlabCollider {
         if ((rc = alloc(&tmp_id, cap))) return rc;
         if ((rc = alloc(&brem, cap))) return rc;
         if ((rc = alloc(&entries, (uint64_t)entries_cap))) return rc;
-        if ((rc = alloc(&state, cap))) return rc;
+        if ((rc = alloc(&head, cap))) return rc;
+        if ((rc = alloc(&chunks, (uint64_t)LIST_CHUNK * cap))) return rc;
+        PS_CUDA_TRY(err, cudaMemsetAsync(head, 0, cap * sizeof(unsigned long long), stream));
         for (int i = 0; i < 3; ++i) if ((rc = alloc(&wl[i], cap))) return rc;
         const size_t hb = halo_bytes<Real>(g.cap_h);
         PS_CUDA_TRY(err, cudaMalloc(&send_l, hb)); PS_CUDA_TRY(err, cudaMalloc(&send_r, hb));
@@ -551,7 +554,7 @@ struct SlabCollider {
         for (auto& p : pid) cudaFree(p);
         for (auto& w : wl) cudaFree(w);
         cudaFree(cell_count); cudaFree(cell_start); cudaFree(scan_sums); cudaFree(slot_cell); cudaFree(arrival);
-        cudaFree(tmp_id); cudaFree(brem); cudaFree(entries); cudaFree(state);
+        cudaFree(tmp_id); cudaFree(brem); cudaFree(entries); cudaFree(head); cudaFree(chunks);
         cudaFree(send_l); cudaFree(send_r); cudaFree(recv_l); cudaFree(recv_r); cudaFree(ds); cudaFree(sd); cudaFree(stage);
         if (hc) cudaFreeHost(hc);
         if (own_stream) cudaStreamDestroy(own_stream);
@@ -622,9 +625,9 @@ struct SlabCollider {
     }
 
     int launch_resolve(const StepConst<Real>& k, uint32_t r0) {
-        Rec<Real>* a_rec = rec[cur ^ 1]; const uint32_t* a_ent = entries; PState* a_head = state;
+        Rec<Real>* a_rec = rec[cur ^ 1]; const uint32_t* a_chunks = chunks; const uint32_t* a_ent = entries; unsigned long long* a_head = head;
         uint2 *a0 = wl[0], *a1 = wl[1], *a2 = wl[2]; StepConst<Real> a_k = k; DevState* a_ds = ds; uint32_t a_r0 = r0;
-        void* args[] = {&a_rec, &a_ent, &a_head, &a0, &a1, &a2, &a_k, &a_ds, &a_r0};
+        void* args[] = {&a_rec, &a_chunks, &a_ent, &a_head, &a0, &a1, &a2, &a_k, &a_ds, &a_r0};
         const uint64_t want = ((uint64_t)g.cap + RESOLVE_THREADS - 1) / RESOLVE_THREADS;
         const unsigned grid = (unsigned)(want < (uint64_t)resolve_grid ? want : (uint64_t)resolve_grid);
         PS_CUDA_TRY(err, cudaLaunchCooperativeKernel((const void*)resolve_kernel<Real>, dim3(grid), dim3(RESOLVE_THREADS), args, 0, stream));
@@ -636,7 +639,13 @@ struct SlabCollider {
         PS_CUDA_TRY(err, cudaMemcpyAsync(&hc->sd, sd, sizeof(SlabDev), cudaMemcpyDeviceToHost, stream));
         PS_CUDA_TRY(err, cudaMemcpyAsync(&hc->ds, ds, sizeof(DevState), cudaMemcpyDeviceToHost, stream));
         PS_CUDA_TRY(err, cudaStreamSynchronize(stream));
+        return check_host_copy();
+    }
+
+    // every device-side flag of this rank, from the host copies `hc` just read
+    int check_host_copy() {
         const uint32_t e = hc->sd.err;
+        if (e & SLAB_ERR_PROTOCOL) return fail(PS_ERR_NCCL, "boundary hand-over sizes disagree between neighbouring ranks");
         if (e & SLAB_ERR_MIGRATION) return fail(PS_ERR_MIGRATION, "a particle crossed a whole neighbouring slab in one sub-step");
         if (e & SLAB_ERR_HALO) return fail(PS_ERR_CAPACITY, "halo / migration buffer too small for this scene");
         if (e & SLAB_ERR_CAPACITY) return fail(PS_ERR_CAPACITY, "this rank's slab holds more particles than it was sized for");
@@ -644,8 +653,8 @@ struct SlabCollider {
                                                      " holds a record in global cell (" + std::to_string(hc->ds.dbg[1]) + "," + std::to_string(hc->ds.dbg[2]) + "), outside local columns [" +
                                                      std::to_string(g.col_off) + "," + std::to_string(g.col_off + g.ncl) + "); sd.err=" + std::to_string(hc->sd.err) +
                                                      " n_own_prev=" + std::to_string(hc->sd.n_own_prev) + " own=[" + std::to_string(hc->sd.own_b) + "," + std::to_string(hc->sd.own_e) + ")");
-        if (hc->ds.flags & FLAG_LIST_TOO_LONG) return fail(PS_ERR_CAPACITY, "one particle has more than 8191 contacts (the per-particle limit of the cursor word); the scene is far denser than the reference's u8 cell counters allow");
-        if (hc->ds.flags & FLAG_CAPACITY) return fail(PS_ERR_CAPACITY, "contact list exceeded its capacity; raise ps_config.contacts_per_particle");
+        if (hc->ds.flags & FLAG_LIST_TOO_LONG) return fail(PS_ERR_CAPACITY, "one particle has more than 8191 contacts (the per-particle limit of the head word); the scene is far denser than the reference's u8 cell counters allow");
+        if (hc->ds.flags & FLAG_CAPACITY) return fail(PS_ERR_CAPACITY, "the overflow pool of the contact lists is full; raise ps_config.contacts_per_particle");
         if (hc->ds.flags & FLAG_CELL_OVERFLOW) return fail(PS_ERR_CELL_OVERFLOW, "a grid cell held more than 255 particles (src/core.zig:51,132)");
         return PS_OK;
     }
@@ -693,15 +702,16 @@ struct SlabCollider {
         if (int d = dbg("move")) return d;
         SlabView sv{g.gl, g.gr, g.ncl, g.col_off, g.gcols, &sd->n_local, &sd->n_blocked, brem};
         const uint64_t n_hi = (uint64_t)n_own_step + 2ull * g.cap_h;             // at most this many local slots after the exchange
-        const unsigned g_det = (unsigned)(((n_hi < g.cap ? n_hi : g.cap) + DETECT_THREADS - 1) / DETECT_THREADS);
-        detect_kernel<Real, true><<<g_det, DETECT_THREADS, 0, st>>>(rec[nw], cell_start, g.cap, k, entries, entries_cap, state, wl[0], ds, sv);
+        const uint64_t n_det = n_hi < g.cap ? n_hi : g.cap;
+        const uint32_t span = detect_span(n_det);
+        detect_kernel<Real, true><<<detect_grid(n_det, span), DETECT_THREADS, 0, st>>>(rec[nw], cell_start, g.cap, span, k, chunks, entries, entries_cap, head, wl[0], ds, sv);
         launches += 9;
         int rc;
         if (int d = dbg("detect")) return d;
         tick(3);
         if ((rc = launch_resolve(k, 0u))) return rc;                              // phase A
         if (int d = dbg("resolve A")) return d;
-        if (g.gr) { slab_right_check_kernel<<<(2 * g.cap_h + 255) / 256, 256, 0, st>>>(state, brem, sd); ++launches; }   // two columns of slots at most
+        if (g.gr) { slab_right_check_kernel<<<(2 * g.cap_h + 255) / 256, 256, 0, st>>>(head, brem, sd); ++launches; }   // two columns of slots at most
         tick(4);
         if ((rc = read_back())) return rc;                                        // the one host synchronisation of the sub-step
         h_step = hc->sd;
@@ -724,7 +734,7 @@ struct SlabCollider {
     int stage_phase_b() {
         cudaStream_t st = stream;
         slab_unpack_kernel<Real><<<(g.cap_h + 255) / 256, 256, 0, st>>>(recv_l, rec[cur ^ 1], &sd->zero, &sd->c_first2, g.cap_h, sd);
-        slab_unblock_kernel<<<(h_step.c_first2 + 255) / 256 + 1, 256, 0, st>>>(state, brem, wl[r0_step % 3], &ds->wl_count[r0_step % 3], r0_step, sd);
+        slab_unblock_kernel<<<(h_step.c_first2 + 255) / 256 + 1, 256, 0, st>>>(head, brem, wl[r0_step % 3], &ds->wl_count[r0_step % 3], r0_step, sd);
         launches += 2;
         if (int d = dbg("unpack+unblock")) return d;
         if (int rc = launch_resolve(k_step, r0_step)) return rc;
@@ -780,13 +790,11 @@ struct SlabCollider {
     }
 
 
+    // Waits for everything queued and reports what the LAST sub-step raised after its one mid-step read-back (phase B's
+    // resolve, a late hand-over): without this a failed final sub-step would look like success.
     int sync() {
         if (err.status != PS_OK) return err.status;
-        PS_CUDA_TRY(err, cudaMemcpyAsync(&hc->sd, sd, sizeof(SlabDev), cudaMemcpyDeviceToHost, stream));
-        PS_CUDA_TRY(err, cudaStreamSynchronize(stream));
-        if (hc->sd.err & SLAB_ERR_PROTOCOL) return fail(PS_ERR_NCCL, "boundary hand-over sizes disagree between neighbouring ranks");
-        if (hc->sd.err & SLAB_ERR_HALO) return fail(PS_ERR_CAPACITY, "halo / migration buffer too small for this scene");
-        return PS_OK;
+        return read_back();
     }
 
     // this rank's owned particles: global indices + interleaved f64 position / velocity

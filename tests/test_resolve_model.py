@@ -2,8 +2,8 @@
 
 The reference resolves its ordered pair list front to back (src/core.zig:211-213).  The kernel instead runs, round
 after round, every pair that heads BOTH of its particles' sub-lists, from work lists that hold only the particles whose
-head moved in the previous round.  This file restates that protocol in Python — same per-particle state (stamp, entries left,
-head entry in one word; cursor and look-ahead entry beside it), same tie-break, same rule for the first work list — executes the items of every round in a random order, and
+head moved in the previous round.  This file restates that protocol in Python — same head word (stamp, position, head entry),
+same fixed chunk + overflow pool for the other entries, same tie-break, same rule for the first work list — executes the items of every round in a random order, and
 checks that the state ends bit-identical to the sequential loop.  Arithmetic: oracle/core_ref.py's resolve_collision.
 """
 from __future__ import annotations
@@ -28,18 +28,40 @@ def sublists(pairs, slot_of, n):
     return lists
 
 
+LIST_CHUNK = 8          # csrc/ps_collide.cuh: entries 1..8 of a sub-list live in the slot's own chunk, entry 0 in its head word
+
+
+def lay_out(lists):
+    """detect_kernel's layout: per slot a chunk of LIST_CHUNK words, plus a pool for the tails of long sub-lists."""
+    chunks, pool = [[None] * LIST_CHUNK for _ in lists], []
+    for a, l in enumerate(lists):
+        ovf = len(l) > LIST_CHUNK + 1
+        if ovf:
+            chunks[a][LIST_CHUNK - 1] = len(pool)                # index of the overflow run
+        for j in range(1, len(l)):
+            e = (l[j], j + 1 == len(l))                          # (entry, LAST)
+            if not ovf or j - 1 < LIST_CHUNK - 1:
+                chunks[a][j - 1] = e
+            else:
+                pool.append(e)
+    return chunks, pool
+
+
+def load_entry(chunks, pool, a, j, ovf):
+    idx = j - 1
+    if not ovf or idx < LIST_CHUNK - 1:
+        return chunks[a][idx]
+    return pool[chunks[a][LIST_CHUNK - 1] + idx - (LIST_CHUNK - 1)]
+
+
 def run_rounds(lists, execute, rng):
     """The rounds of resolve_kernel.  execute(i_slot, j_slot) resolves one pair {i = neighbour, j = centre}.
 
-    Per particle, as in the kernel's 16-byte state: [stamp, entries left, head entry] (one 64-bit word, the only thing a
-    readiness test looks at) plus cursor and the entry after the head (touched only by the thread that runs the pair)."""
+    Per particle one head word [stamp, pos, live, ovf, last, entry]: a readiness test looks at the two head words only;
+    the thread that runs the pair fetches each particle's next entry from that particle's chunk (or the pool)."""
     n = len(lists)
-    entries, begin = [], []
-    for l in lists:                                              # `entries`: the sub-lists back to back, as detect lays them out
-        begin.append(len(entries))
-        entries.extend(l)
-    none = (0, 0)
-    state = [[0, len(l), l[0] if l else none, begin[a], l[1] if len(l) > 1 else none] for a, l in enumerate(lists)]
+    chunks, pool = lay_out(lists)
+    head = [[0, 0, bool(l), len(l) > LIST_CHUNK + 1, len(l) == 1, l[0] if l else None] for l in lists]
     # detect_kernel: on the first list only if the first partner has a higher slot (round 0 runs pairs from the lower slot)
     work = [(a, lists[a][0]) for a in range(n) if lists[a] and lists[a][0][0] > a]
     r, executed = 0, 0
@@ -50,28 +72,28 @@ def run_rounds(lists, execute, rng):
             b, a_centre = ea
             if r == 0 and b < a:
                 continue
-            sa, rem_a, head_a, cur_a, next_a = state[a]
-            sb, rem_b, head_b, cur_b, next_b = state[b]
-            if sa == r + 1 or sb == r + 1 or rem_b == 0:
+            sa, pos_a, live_a, ovf_a, last_a, ent_a = head[a]
+            sb, pos_b, live_b, ovf_b, last_b, ent_b = head[b]
+            if sa == r + 1 or sb == r + 1 or not live_b:
                 continue
-            if head_b != (a, 1 - a_centre):                      # not the same pair seen from the other side
+            if ent_b != (a, 1 - a_centre):                       # not the same pair seen from the other side
                 continue
             if b < a and sb == r:                                # both on this round's list: the lower slot runs it
                 continue
-            assert head_a == ea and entries[cur_a] == ea and entries[cur_b] == head_b
-            nn_a = entries[cur_a + 2] if rem_a > 2 else none     # the entries that become `next` after the advance
-            nn_b = entries[cur_b + 2] if rem_b > 2 else none
+            assert live_a and ent_a == ea and lists[a][pos_a] == ea and lists[b][pos_b] == ent_b
+            na = None if last_a else load_entry(chunks, pool, a, pos_a + 1, ovf_a)
+            nb = None if last_b else load_entry(chunks, pool, b, pos_b + 1, ovf_b)
             execute(b, a) if a_centre else execute(a, b)
             executed += 1
-            state[a] = [r + 1, rem_a - 1, next_a if rem_a > 1 else none, cur_a + 1, nn_a]
-            state[b] = [r + 1, rem_b - 1, next_b if rem_b > 1 else none, cur_b + 1, nn_b]
-            if rem_a > 1:
-                nxt.append((a, next_a))
-            if rem_b > 1:
-                nxt.append((b, next_b))
+            head[a] = [r + 1, pos_a + 1, na is not None, ovf_a, bool(na and na[1]), na[0] if na else None]
+            head[b] = [r + 1, pos_b + 1, nb is not None, ovf_b, bool(nb and nb[1]), nb[0] if nb else None]
+            if na:
+                nxt.append((a, na[0]))
+            if nb:
+                nxt.append((b, nb[0]))
         work = nxt
         r += 1
-    assert all(st[1] == 0 for st in state), "some sub-list was not drained"
+    assert all(not h[2] and h[1] == len(l) for h, l in zip(head, lists)), "some sub-list was not drained"
     return r, executed
 
 

@@ -20,7 +20,7 @@ from particle_simulator_b200 import capi
 
 pytestmark = pytest.mark.gpu
 
-MAX_CELLS = 16384 * 4096
+MAX_CELLS = 16384 * 4096          # PS_STATIC_SCAN_MAX_CELLS in include/particles_cuda.h
 
 
 def _run(fn, grid: np.ndarray):
@@ -48,6 +48,37 @@ def test_static_variant_equals_allocating_variant_twice_in_a_row():
         got = _run(L.ps_compute_start_array_static, grid)
         assert np.array_equal(got, want)
         assert int(got[-1]) == int(grid.sum(dtype=np.uint64) & 0xFFFFFFFF)
+
+
+def test_static_variant_takes_no_device_memory():
+    """The point of the entry point: after its first call on the device (which looks up the built-in array), further
+    calls leave the amount of free device memory exactly where it was, also for a size it has not seen before."""
+    import torch
+
+    L = capi.load()
+    rng = np.random.default_rng(3)
+    d_in = torch.from_numpy(rng.integers(0, 9, size=3_000_001, dtype=np.uint32).view(np.int32)).cuda()
+    d_out = torch.empty(d_in.numel() + 1, dtype=torch.int32, device="cuda")
+    stream = torch.cuda.current_stream().cuda_stream
+    call = lambda cells: L.ps_compute_start_array_static(ctypes.c_void_p(d_in.data_ptr()), ctypes.c_void_p(d_out.data_ptr()), cells, ctypes.c_void_p(stream))
+    assert call(1000) == capi.PS_OK                      # set-up call
+    torch.cuda.synchronize()
+    free0, _ = torch.cuda.mem_get_info()
+    for cells in (3_000_001, 12_345, 2_000_000):
+        assert call(cells) == capi.PS_OK
+        torch.cuda.synchronize()
+        assert torch.cuda.mem_get_info()[0] == free0
+    want = np.concatenate([[0], np.cumsum(d_in[:2_000_000].cpu().numpy().view(np.uint32), dtype=np.uint64)]).astype(np.uint32)
+    assert np.array_equal(d_out[:2_000_001].cpu().numpy().view(np.uint32), want)
+
+
+def test_header_exports_the_limit():
+    import os
+    import re
+
+    text = open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "include", "particles_cuda.h")).read()
+    m = re.search(r"#define\s+PS_STATIC_SCAN_MAX_CELLS\s+(\d+)ull", text)
+    assert m and int(m.group(1)) == MAX_CELLS
 
 
 def test_static_variant_rejects_sizes_beyond_its_scratch():

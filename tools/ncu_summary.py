@@ -29,6 +29,16 @@ KEEP = [
 BYTES = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12}
 
 
+def measured_peak():
+    """hbm_gbs of MEASURED_PEAKS.json at the repo root (the one source of the roofline denominator); fallback as B200_PROFILING.md states."""
+    import os
+    try:
+        with open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"])
+    except Exception:
+        return 6650.0
+
+
 def launches(path, out, algo=None):
     with open(path) as fh:
         lines = [l for l in fh if not l.startswith("==")]
@@ -107,7 +117,7 @@ if __name__ == "__main__":
             def opt(name, default):
                 return float(sys.argv[sys.argv.index(name) + 1]) if name in sys.argv else default
             algo = {"particles": int(opt("--particles", 0)), "cells": int(opt("--cells", 0)), "pairs": int(opt("--pairs", 0)),
-                    "peak": opt("--peak", 6442.6)}
+                    "peak": opt("--peak", measured_peak())}
         launches(sys.argv[2], sys.argv[3], algo)
     else:
         tj = sys.argv[sys.argv.index("--traffic-json") + 1] if "--traffic-json" in sys.argv else None
