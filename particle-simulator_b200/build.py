@@ -14,7 +14,9 @@ PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(PKG_DIR)
 CSRC = os.path.join(PKG_DIR, "csrc")
 INCLUDE = os.path.join(ROOT, "include")
-LIB_PATH = os.path.join(PKG_DIR, "libparticles_cuda.so")
+# PS_LIB=<path> (developer hook): load / build another file instead, e.g. an instrumented build made with
+# PS_NVCC_EXTRA="-DPS_TAIL_PROFILE"; the product is always libparticles_cuda.so beside this file.
+LIB_PATH = os.environ.get("PS_LIB") or os.path.join(PKG_DIR, "libparticles_cuda.so")
 HEADLESS_PATH = os.path.join(PKG_DIR, "ps_headless")
 
 NVCC_FLAGS = [
@@ -53,7 +55,7 @@ def build_lib(force: bool = False, verbose: bool = False) -> str:
     if not force and not _stale(LIB_PATH, srcs):
         return LIB_PATH
     cus = [s for s in srcs if s.endswith(".cu")]
-    cmd = [_nvcc(), *NVCC_FLAGS, "-shared", "-o", LIB_PATH, *cus, "-lcudart"]
+    cmd = [_nvcc(), *NVCC_FLAGS, *os.environ.get("PS_NVCC_EXTRA", "").split(), "-shared", "-o", LIB_PATH, *cus, "-lcudart"]
     if verbose:
         cmd.insert(1, "-Xptxas=-v")
         print(" ".join(cmd), file=sys.stderr)

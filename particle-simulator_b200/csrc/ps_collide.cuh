@@ -716,6 +716,25 @@ __device__ __forceinline__ void resolve_pair(Rec<Real>& I, Rec<Real>& J, const S
     J.u = J.u + nx * kk; J.w = J.w + ny * kk;                                 // :391
 }
 
+// -DPS_TAIL_PROFILE (developer builds only, tools/tail_profile.sh): thread 0 of the tail CTA accumulates the clock cycles
+// between marks along one tail round and prints the sums when the kernel ends.
+#ifdef PS_TAIL_PROFILE
+#define PS_MARK(i) do { if (LOCAL && threadIdx.x == 0) { const long long t__ = clock64(); prof[i] += t__ - prof[15]; prof[15] = t__; ++prof[14 - ((i) == 6)]; } } while (0)
+#define PS_PROF_PARAM , long long (&prof)[16]
+#define PS_PROF_ARG , prof
+__device__ __forceinline__ void ps_keep(uint32_t x) { asm volatile("" :: "r"(x)); }
+__device__ __forceinline__ void ps_keep(float x) { asm volatile("" :: "f"(x)); }
+__device__ __forceinline__ void ps_keep(double x) { asm volatile("" :: "d"(x)); }
+#define PS_KEEP(x) ps_keep(x)
+#define PS_PROF_DUMMY long long prof[16] = {}; (void)prof;
+#else
+#define PS_PROF_DUMMY
+#define PS_MARK(i) do {} while (0)
+#define PS_PROF_PARAM
+#define PS_PROF_ARG
+#define PS_KEEP(x) do {} while (0)
+#endif
+
 constexpr int RESOLVE_THREADS = 1024;     // one CTA per SM in the grid phase: the grid barrier has 148 participants
 constexpr int RESOLVE_TAIL_THREADS = 256; // the single-CTA tail keeps 8 warps (a CTA barrier among 32 warps is slower)
 constexpr uint32_t RESOLVE_TAIL = 512;    // work lists this short are finished by one CTA out of shared memory (deep chains: hundreds of short rounds)
@@ -730,7 +749,7 @@ constexpr uint32_t RESOLVE_TAIL_CAP = 2 * RESOLVE_TAIL;   // a round appends at 
 // L1 hits cut the per-round latency.  (Nothing was loaded through L1 earlier in the kernel, so no stale lines exist.)
 template <class Real, bool LOCAL>
 __device__ __forceinline__ int resolve_item(Rec<Real>* rec, const uint32_t* __restrict__ chunks, const uint32_t* __restrict__ pool,
-                                            unsigned long long* head, uint2 item, uint32_t r, const StepConst<Real>& k, uint2 (&next)[2]) {
+                                            unsigned long long* head, uint2 item, uint32_t r, const StepConst<Real>& k, uint2 (&next)[2] PS_PROF_PARAM) {
     const uint32_t a = item.x, ea = item.y;
     const uint32_t b = ea & ENT_SLOT_MASK;
     // Round 0: every particle with a visible list is on the work list, and a pair can only be ready if the two
@@ -742,6 +761,7 @@ __device__ __forceinline__ int resolve_item(Rec<Real>* rec, const uint32_t* __re
     const unsigned long long hb = LOCAL ? head[b] : __ldcg(head + b);
     const Rec<Real> Ra = LOCAL ? ld_rec(rec + a) : ld_rec_cg(rec + a), Rb = LOCAL ? ld_rec(rec + b) : ld_rec_cg(rec + b);
     if (head_stamp(ha) == r + 1) return 0;           // a already ran a pair this round (executed by its partner)
+    PS_MARK(2);
     if (head_stamp(hb) == r + 1) return 0;           // b moved this round; b is on the next list and will look at a
     const uint32_t wa = head_low(ha), wb = head_low(hb);
     if (!(wb & HEAD_LIVE)) return 0;                 // (a is live: it is on the list)
@@ -751,18 +771,23 @@ __device__ __forceinline__ int resolve_item(Rec<Real>* rec, const uint32_t* __re
     // lower slot runs the pair.  Membership is read from the SAME 64-bit word as the head entry, so a
     // concurrent executor cannot make the two threads disagree.
     if (b < a && head_stamp(hb) == r) return 0;
+    PS_MARK(3);
     // the two particles' next entries (requested now, needed only when the head words are written back)
     const uint32_t pos_a = head_pos(ha), pos_b = head_pos(hb);
     const bool more_a = !(wa & ENT_LAST), more_b = !(wb & ENT_LAST);
     const uint32_t na = more_a ? (load_entry(chunks, pool, a, pos_a + 1u, wa & HEAD_OVF) | HEAD_LIVE | (wa & HEAD_OVF)) : 0u;
     const uint32_t nb = more_b ? (load_entry(chunks, pool, b, pos_b + 1u, wb & HEAD_OVF) | HEAD_LIVE | (wb & HEAD_OVF)) : 0u;
+    PS_KEEP(na); PS_KEEP(nb); PS_MARK(4);
     const bool a_centre = (ea >> ENT_ROLE_BIT) & 1u; // entry = {particle_i = neighbour, particle_j = centre}
     Rec<Real> I = a_centre ? Rb : Ra, J = a_centre ? Ra : Rb;
+    PS_KEEP(I.x); PS_KEEP(J.x); PS_MARK(5);
     resolve_pair<Real>(I, J, k);
+    PS_KEEP(I.u); PS_KEEP(J.u); PS_KEEP(I.x); PS_MARK(6);
     st_rec(rec + (a_centre ? b : a), I);
     st_rec(rec + (a_centre ? a : b), J);
     head[a] = head_word(r + 1, pos_a + 1u, na);
     head[b] = head_word(r + 1, pos_b + 1u, nb);
+    PS_MARK(7);
     const uint2 ia = make_uint2(a, na), ib = make_uint2(b, nb);     // (constant indices keep `next` in registers)
     next[0] = more_a ? ia : ib;
     next[1] = ib;
@@ -782,7 +807,8 @@ __device__ __forceinline__ void resolve_round(Rec<Real>* rec, const uint32_t* __
         const uint32_t idx = base + threadIdx.x;
         if (idx < cnt) {
             uint2 next[2];
-            const int m = resolve_item<Real, false>(rec, chunks, pool, head, __ldcg(wl + idx), r, k, next);
+            PS_PROF_DUMMY
+            const int m = resolve_item<Real, false>(rec, chunks, pool, head, __ldcg(wl + idx), r, k, next PS_PROF_ARG);
             for (int i = 0; i < m; ++i) sh_buf[atomicAdd(sh_cnt, 1u)] = next[i];
         }
         __syncthreads();
@@ -825,7 +851,8 @@ __device__ __forceinline__ void resolve_round_warps(Rec<Real>* rec, const uint32
         const uint32_t ahead = idx + stride;
         if (ahead < cnt) item = __ldcg(wl + ahead);
         uint2 next[2];
-        const int m = live ? resolve_item<Real, false>(rec, chunks, pool, head, cur, r, k, next) : 0;
+        PS_PROF_DUMMY
+        const int m = live ? resolve_item<Real, false>(rec, chunks, pool, head, cur, r, k, next PS_PROF_ARG) : 0;
         const uint32_t one = __ballot_sync(0xffffffffu, m >= 1), two = __ballot_sync(0xffffffffu, m >= 2);
         if (one) {
             const uint32_t below = (1u << lane) - 1u;
@@ -870,15 +897,21 @@ resolve_kernel(Rec<Real>* rec, const uint32_t* __restrict__ chunks, const uint32
     // Tail phase: CTA 0 alone.  A settled pile has hundreds of short rounds whose cost is the chain "read the two
     // particles - resolve - write them back - tell the other threads", so a round here costs ONE CTA barrier and nothing
     // else that is shared: the work list lives in shared memory (three rotating buffers carved out of the grid phase's
-    // append buffers, with their lengths beside them), items are appended with one shared-memory atomic per warp, and
+    // append buffers, with their lengths beside them), items are appended with one shared-memory atomic per executed pair, and
     // the particles' records and states are served by this SM's L1 (plain loads; the barrier makes the CTA's own
     // writes visible).  A list that outgrows the buffers (rare) goes back to global memory for a round.
+#ifdef PS_TAIL_PROFILE
+    constexpr bool LOCAL = true;
+    long long prof[16] = {};
+    prof[15] = clock64();
+#endif
     uint2* const tl_items = sh_buf;                          // [3][RESOLVE_TAIL_CAP]
     __shared__ uint32_t tl_n[3];
-    const uint32_t lane = threadIdx.x & 31u;
-    bool in_smem = false;
+    bool in_smem = false, rot_valid = false;
+    uint32_t cur = 0, nxt = 0, nn = 0;
     for (;;) {
         if (!in_smem) {
+            rot_valid = false;
             const uint32_t cur = r % 3, nxt = (r + 1) % 3, nn = (r + 2) % 3;
             const uint32_t cnt = __ldcg(&ds->wl_count[cur]);
             if (trace && r < 64) { ds->trace_cnt[r] = cnt; ds->trace_ns[r] = (uint32_t)(global_ns() - t_begin); }
@@ -899,9 +932,8 @@ resolve_kernel(Rec<Real>* rec, const uint32_t* __restrict__ chunks, const uint32
             ++r;
             continue;
         }
-        const uint32_t cur = r % 3, nxt = (r + 1) % 3, nn = (r + 2) % 3;
+        if (!rot_valid) { cur = r % 3; nxt = (r + 1) % 3; nn = (r + 2) % 3; rot_valid = true; }
         const uint32_t cnt = tl_n[cur];
-        if (trace && r < 64) { ds->trace_cnt[r] = cnt; ds->trace_ns[r] = (uint32_t)(global_ns() - t_begin); }
         if (cnt == 0 || r + 2 >= HEAD_STAMP_MAX) break;
         if (cnt > RESOLVE_TAIL) {                            // grew beyond what the next round's appends could hold: back to global memory
             for (uint32_t i = threadIdx.x; i < cnt; i += RESOLVE_TAIL_THREADS) list(cur)[i] = tl_items[cur * RESOLVE_TAIL_CAP + i];
@@ -911,26 +943,31 @@ resolve_kernel(Rec<Real>* rec, const uint32_t* __restrict__ chunks, const uint32
             __syncthreads();
             continue;
         }
+        PS_MARK(0);
         if (threadIdx.x == 0) tl_n[nn] = 0;                  // the input of round r-1; everybody read it before that round's barrier
         const uint2* in = tl_items + cur * RESOLVE_TAIL_CAP;
         uint2* out = tl_items + nxt * RESOLVE_TAIL_CAP;
-        for (uint32_t idx = threadIdx.x; idx - lane < cnt; idx += RESOLVE_TAIL_THREADS) {   // whole warps: the ballots below need every lane
+        for (uint32_t idx = threadIdx.x; idx < cnt; idx += RESOLVE_TAIL_THREADS) {
             uint2 next[2];
-            const int m = idx < cnt ? resolve_item<Real, true>(rec, chunks, pool, head, in[idx], r, k, next) : 0;
-            const uint32_t one = __ballot_sync(0xffffffffu, m >= 1), two = __ballot_sync(0xffffffffu, m >= 2);
-            if (one) {
-                uint32_t base = 0;
-                if (lane == 0) base = atomicAdd(&tl_n[nxt], (uint32_t)__popc(one) + (uint32_t)__popc(two));
-                base = __shfl_sync(0xffffffffu, base, 0);
-                const uint32_t below = (1u << lane) - 1u;
-                const uint32_t at = base + (uint32_t)__popc(one & below) + (uint32_t)__popc(two & below);
-                if (m >= 1) out[at] = next[0];
-                if (m >= 2) out[at + 1] = next[1];
+            PS_MARK(1);
+            const int m = resolve_item<Real, true>(rec, chunks, pool, head, in[idx], r, k, next PS_PROF_ARG);
+            if (m) {                                         // (a shared-memory atomic per executed pair: no warp-wide vote, lanes stay independent)
+                const uint32_t at = atomicAdd(&tl_n[nxt], (uint32_t)m);
+                out[at] = next[0];
+                if (m == 2) out[at + 1] = next[1];
             }
         }
+        PS_MARK(8);
         __syncthreads();                                     // the round's one barrier: global writes and appended items become visible
+        PS_MARK(9);
         ++r;
+        { const uint32_t t = cur; cur = nxt; nxt = nn; nn = t; }      // (r % 3 without the divisions: this loop is one long dependent chain)
     }
+#ifdef PS_TAIL_PROFILE
+    if (threadIdx.x == 0 && ds->trace_on && r_start == 0)
+        printf("[tail profile] rounds %u marks(top,item,heads,decided,entries,operands,computed,stored,appended,barrier) %lld %lld %lld %lld %lld %lld %lld %lld %lld %lld  passes %lld executed %lld\n",
+               r, prof[0], prof[1], prof[2], prof[3], prof[4], prof[5], prof[6], prof[7], prof[8], prof[9], prof[14], prof[13]);
+#endif
     uint32_t left = 0;
     if (threadIdx.x == 0) left = in_smem ? tl_n[r % 3] : __ldcg(&ds->wl_count[r % 3]);
     if (threadIdx.x == 0) {
