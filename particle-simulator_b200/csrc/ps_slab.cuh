@@ -866,11 +866,16 @@ struct SlabGroupLocal {
             if (k + 1 < n && (rc = copy(ranks[k + 1]->recv_l, ranks[k + 1], ranks[k]->send_r, ranks[k]))) return rc;
         }
         for (auto* r : ranks) if ((rc = r->stage_build())) { err = r->err; return rc; }
-        for (int k = 0; k < n; ++k) {                                               // M1 chain, left to right
+        // M1 chain, left to right, in the order the multi-process path queues it on each rank: a rank whose right boundary was
+        // complete after phase A packs its hand-over BEFORE its own phase B (the branch every interior rank of a production
+        // run takes), otherwise after it.
+        for (int k = 0; k < n; ++k) {
             auto* r = ranks[k];
+            const bool early = k + 1 < n && r->send_now_step;
+            if (early && (rc = r->pack_m1())) { err = r->err; return rc; }
             if (k > 0 && (rc = r->stage_phase_b())) { err = r->err; return rc; }
             if (k + 1 < n) {
-                if ((rc = r->pack_m1())) { err = r->err; return rc; }
+                if (!early && (rc = r->pack_m1())) { err = r->err; return rc; }
                 if ((rc = copy(ranks[k + 1]->recv_l, ranks[k + 1], r->send_r, r))) return rc;
             }
         }

@@ -93,6 +93,43 @@ def test_emulated_ranks_dense_narrow_slabs():
     assert_bit_exact(got_v, want_v, "velocities")
 
 
+def dense_band_scene(count=6000, seed=9):
+    """Far from uniform: most particles in a band astride the boundary between two slabs (8 ranks of the default world:
+    22-23 cell columns each, boundaries at x = 88, 180, 268, ...), falling under gravity."""
+    scene = scenes.default_scene().with_(count=count)
+    rng = np.random.default_rng(seed)
+    pos = np.empty((count, 2))
+    vel = rng.uniform(-200.0, 200.0, size=(count, 2))
+    band = rng.random(count) < 0.8
+    pos[:, 0] = np.where(band, np.clip(rng.normal(180.0, 25.0, count), scene.radius, scene.width - scene.radius),
+                         rng.uniform(scene.radius, scene.width, count))
+    pos[:, 1] = rng.uniform(scene.radius, scene.height, count)
+    return scene, np.ascontiguousarray(pos), np.ascontiguousarray(vel)
+
+
+@pytest.mark.parametrize("nranks,precision", [(8, "f64"), (4, "f32")])
+def test_emulated_ranks_dense_band_under_gravity(nranks, precision):
+    """Non-uniform load: a dense band on a slab boundary with gravity on (the penalty branch of resolve_collision, long
+    dependency chains that run across the boundary, ranks holding several times the average share)."""
+    from particle_simulator_b200 import SlabGroup
+
+    dtype = np.float64 if precision == "f64" else np.float32
+    scene, pos0, vel0 = dense_band_scene()
+    want_p, want_v, out = run_oracle(scene, pos0.astype(dtype), vel0.astype(dtype), 480, collisions=True, t_acc=True)
+    with SlabGroup(scene, nranks, precision=precision, contacts_per_particle=96) as g:
+        g.upload_global(pos0, vel0)
+        g.set_acc(True)
+        g.step_substeps(480)
+        parts = [g.download_owned(r) for r in range(nranks)]
+        pairs = sum(g.stats(r)["pairs_total"] for r in range(nranks))
+    got_p, got_v = gather(parts, scene.count, dtype)
+    assert pairs == out["stats"]["pairs_total"]
+    assert_bit_exact(got_p, want_p, "positions")
+    assert_bit_exact(got_v, want_v, "velocities")
+    counts = [len(ids) for ids, _, _ in parts]
+    assert max(counts) > 3 * (scene.count // nranks) // 2, "the scene was meant to be unbalanced"
+
+
 def _two_rank_worker(rank, world, port, tmpdir, case):
     import torch
     import torch.distributed as dist
@@ -108,8 +145,11 @@ def _two_rank_worker(rank, world, port, tmpdir, case):
     scene, seed, substeps, precision, t_acc = case[:5]
     if len(case) > 5 and case[5]:
         os.environ["PS_SLAB_FORCE_LATE"] = "1"      # every rank sends its boundary states only after its own phase B
-    pos0, vel0 = scenes.spawn(scene, seed=seed)
-    with SlabSimulation(scene, rank, world, bytes(idt.numpy().tobytes()), precision=precision, device=rank, contacts_per_particle=32) as s:
+    if isinstance(scene, str):
+        scene, pos0, vel0 = dense_band_scene(seed=seed)
+    else:
+        pos0, vel0 = scenes.spawn(scene, seed=seed)
+    with SlabSimulation(scene, rank, world, bytes(idt.numpy().tobytes()), precision=precision, device=rank, contacts_per_particle=96) as s:
         s.upload_global(pos0, vel0)
         s.set_acc(t_acc)
         s.step_substeps(substeps)
@@ -127,6 +167,7 @@ CASES = {
     "dense_narrow": (scenes.Scene(count=3000, width=64.0, height=400.0), 3, 150, "f64", False),   # 16 columns: 8 per rank
     "one_million": (scenes.scaled_scene(1 << 20), 1, 24, "f32", False),
     "late_boundary_path": (scenes.default_scene(), 5, 120, "f64", True, True),
+    "dense_band_gravity": ("dense_band", 9, 320, "f64", True),
 }
 
 
@@ -143,7 +184,10 @@ def test_two_ranks_equal_oracle(name, world, tmp_path):
     dtype = np.float64 if precision == "f64" else np.float32
     port = 29600 + (os.getpid() % 1000)
     mp.spawn(_two_rank_worker, args=(world, port, str(tmp_path), case), nprocs=world, join=True)
-    pos0, vel0 = scenes.spawn(scene, seed=seed)
+    if isinstance(scene, str):
+        scene, pos0, vel0 = dense_band_scene(seed=seed)
+    else:
+        pos0, vel0 = scenes.spawn(scene, seed=seed)
     want_p, want_v, out = run_oracle(scene, pos0.astype(dtype), vel0.astype(dtype), substeps, collisions=True, t_acc=t_acc)
     parts, pairs = [], 0
     for r in range(world):
