@@ -45,6 +45,7 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-extras", action="store_true")
+    ap.add_argument("--watchdog", type=int, default=780, help="seconds after which a stuck run dumps its stacks and exits (0 = off)")
     ap.add_argument("--no-f64", action="store_true", help="skip the f64 build's roofline / end-to-end figures")
     ap.add_argument("--no-collide", action="store_true", help="skip the collision scenes (BASELINE.json configs[3], configs[4])")
     ap.add_argument("--collide-particles", type=int, default=256 << 20, help="particles of the configs[4] collision scene (whole scene, all GPUs)")
@@ -77,8 +78,11 @@ def env_int(name, default):
         return default
 
 
+T_START = time.time()
+
+
 def log(*a):
-    print(*a, file=sys.stderr, flush=True)
+    print(f"[{time.time() - T_START:7.1f}s]", *a, file=sys.stderr, flush=True)
 
 
 def spawn_chunked(scene, seed, start, count, dtype, out_pos, out_vel):
@@ -346,6 +350,7 @@ def run_ours(args):
         sim.debug_set_integrate_variant(args.variant)
 
     # ---- device-resident: value + roofline
+    log(f"[rank {rank}] integrate: device-resident timing")
     timed(torch, dist, lambda: sim.step(1), W)
     l0 = sim.stats()["kernel_launches"]
     clocks.start()
@@ -358,6 +363,7 @@ def run_ours(args):
 
     # ---- the f64 build of the same kernel (core.zig as written, src/core.zig:5): its own roofline figures
     roof64 = None
+    log(f"[rank {rank}] integrate: f64 build and end-to-end legs")
     if prec == "f32" and not args.no_f64:
         with Simulation(scene, precision="f64", collisions=False, device=local) as s64:
             s64.set_stream(stream)
@@ -437,7 +443,9 @@ def run_ours(args):
     # ---- the collision-bearing configurations (BASELINE.json configs[3] and configs[4]); every rank takes part
     collide = None
     if not args.no_collide:
+        log(f"[rank {rank}] collision scenes")
         collide = collide_block(torch, dist, args, rank, world, local)
+        log(f"[rank {rank}] collision scenes done")
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -575,8 +583,10 @@ def collide_block(torch, dist, args, rank, world, local):
     key = "collide_256Mi" if n_big == 256 << 20 else f"collide_{n_big >> 20}Mi"
     try:
         sim = new_slab(scene) if world > 1 else Simulation(scene, precision=prec, collisions=True, device=local)
+        log(f"[rank {rank}] {key}: handle created")
         try:
             sim.spawn(1)
+            log(f"[rank {rank}] {key}: spawned")
             blk = time_collision_scene(torch, dist, sim, scene, frames, 2, world, prec, local)
             blk["scaling"] = "strong"
             blk["workload"] = (f"{n_big >> 20}Mi particles, one scene on {world} GPU(s), full updatePhysics with uniform-grid collisions "
@@ -606,6 +616,7 @@ def collide_block(torch, dist, args, rank, world, local):
 
     # ---- N > 1: the NCCL path against the oracle, bit for bit
     if world > 1:
+        log(f"[rank {rank}] slab parity check")
         out["slab_parity"] = slab_parity(torch, dist, gloo, rank, world, local, new_slab, prec)
         if key in out and "error" not in out[key]:
             out[key]["slab_parity"] = out["slab_parity"]["result"]
@@ -839,6 +850,12 @@ def run_collide(args):
 
 def main():
     args = parse_args()
+    # A rank that waits for ever (a peer that died, a message that never comes) would hold the whole box until the
+    # driver's limit: after --watchdog seconds every rank dumps its Python stacks to stderr and exits non-zero.
+    import faulthandler
+
+    if args.watchdog > 0:
+        faulthandler.dump_traceback_later(args.watchdog, exit=True)
     # The contract is ONE JSON line on stdout.  Libraries loaded later write there too (NCCL prints its version banner
     # to fd 1), so everything else is sent to stderr and only the JSON line goes to the real stdout.
     sys.stdout.flush()
