@@ -404,7 +404,8 @@ struct OwnFlags { bool a_own, l_own, r_own; };   // which columns of the 3x3 blo
                                 // 5 or 8 CTAs per SM (48 / 32 registers): +4 % / -1 %; 128- or 512-thread CTAs: +4 % / +3 %
 #endif
 #ifndef PS_DETECT_MINB
-#define PS_DETECT_MINB 6
+#define PS_DETECT_MINB 8      // CTAs of 256 threads per SM (fp32): the kernel waits on loads, so residency beats registers (measured at 16 Mi
+                              // particles, whole sub-step: 5 -> 1.147 ms, 6 -> 1.117 ms, 8 -> 1.106 ms)
 #endif
 #ifndef PS_DETECT_THREADS
 #define PS_DETECT_THREADS 256
@@ -934,6 +935,7 @@ resolve_kernel(Rec<Real>* rec, const uint32_t* __restrict__ chunks, const uint32
         }
         if (!rot_valid) { cur = r % 3; nxt = (r + 1) % 3; nn = (r + 2) % 3; rot_valid = true; }
         const uint32_t cnt = tl_n[cur];
+        if (trace && r < 64) { ds->trace_cnt[r] = cnt; ds->trace_ns[r] = (uint32_t)(global_ns() - t_begin); }
         if (cnt == 0 || r + 2 >= HEAD_STAMP_MAX) break;
         if (cnt > RESOLVE_TAIL) {                            // grew beyond what the next round's appends could hold: back to global memory
             for (uint32_t i = threadIdx.x; i < cnt; i += RESOLVE_TAIL_THREADS) list(cur)[i] = tl_items[cur * RESOLVE_TAIL_CAP + i];
