@@ -506,7 +506,10 @@ def run_ours(args):
 def substep_algorithmic_bytes(n, cells, pairs, precision):
     """Algorithmic bytes of one collision sub-step: the sum over its kernels."""
     rec = 16 if precision == "f32" else 32                      # one record {x, y, u, w}
-    return n * ((rec + 8) + 16 + (2 * rec + 16) + (rec + 12)) + 6 * cells + pairs * (4 * rec + 36)
+    # bin (record in, cell + arrival out), place (12 in, 4 out), move (record + 12 in, record + 4 out), detect (record in, ~4 out:
+    # head words and first-list items of the particles that touch something), scans (6 per cell), resolve (two records and two
+    # head words in and out + list items per executed pair)
+    return n * ((rec + 8) + 16 + (2 * rec + 16) + (rec + 4)) + 6 * cells + pairs * (4 * rec + 36)
 
 
 def scene_cells(scene):

@@ -62,7 +62,7 @@ def launches(path, out, algo=None):
         if algo:
             # algorithmic bytes of the collision kernels (fp32 records), DESIGN.md section 4: per particle, per cell or per listed pair
             per = {"bin_kernel": ("particle", 24), "place_kernel": ("particle", 16), "move_kernel": ("particle", 48),
-                   "scan_reduce_kernel": ("cell", 1), "scan_down_kernel": ("cell", 5), "detect_kernel": ("particle", 28),
+                   "scan_reduce_kernel": ("cell", 1), "scan_down_kernel": ("cell", 5), "detect_kernel": ("particle", 20),
                    "resolve_kernel": ("pair", 100), "integrate_bounce_kernel": ("particle", 32)}
             f.write(f"\nPer kernel against the HBM roofline ({algo['particles']} particles, {algo['cells']} cells, {algo['pairs']} listed pairs; "
                     f"peak {algo['peak']} GB/s measured copy bandwidth):\n\n")
