@@ -40,8 +40,6 @@ constexpr uint32_t SLAB_ERR_MIGRATION = 1u;   // a particle crossed a whole neig
 constexpr uint32_t SLAB_ERR_HALO = 2u;        // halo / migration buffer too small
 constexpr uint32_t SLAB_ERR_CAPACITY = 4u;    // more local particles than the handle was sized for
 constexpr uint32_t SLAB_ERR_PROTOCOL = 8u;    // boundary hand-over sizes disagree between ranks
-constexpr uint32_t SLAB_ERR_FAST = 16u;       // a particle far from the slab boundary reached it within one sub-step (more than two cell columns)
-constexpr uint32_t SLAB_EDGE_COLS = 4;        // local columns on each side whose particles are binned before the halo exchange starts
 
 struct SlabGeom {
     uint32_t rows, gcols;      // global grid
@@ -62,9 +60,7 @@ struct SlabDev {               // device-side counters, copied to the host once 
     uint32_t n_own_prev;       // owned particles at the start of this sub-step
     uint32_t zero;             // always 0 (range start for the pack / unpack kernels)
     uint32_t own_b_prev;       // first owned slot of the layout this sub-step started from
-    uint32_t c_edge_l, c_edge_r; // cell_start at local columns SLAB_EDGE_COLS and ncl - SLAB_EDGE_COLS: owned slots outside [c_edge_l, c_edge_r)
-                               // are the only ones that can reach a neighbour in the next sub-step (see stage_bin_edges)
-    uint32_t vmax_bits;        // largest |velocity component| seen by this sub-step's bin, as float bits (non-negative floats order like integers)
+    uint32_t pad[3];
 };
 
 // halo / migration message: header + records + particle indices
@@ -157,7 +153,6 @@ slab_begin_kernel(SlabDev* __restrict__ sd, DevState* __restrict__ ds, void* sen
         sd->n_own_prev = sd->own_e - sd->own_b;
         sd->own_b_prev = sd->own_b;
         sd->right_incomplete = 0;
-        sd->vmax_bits = 0;
         ds->entries_used = 0;
         ds->pool_used = 0;
         reinterpret_cast<HaloHeader*>(send_l)->count = 0;
@@ -168,22 +163,18 @@ slab_begin_kernel(SlabDev* __restrict__ sd, DevState* __restrict__ ds, void* sen
 // integrate + bounce, local cell + count for particles that stay in the local grid, migrants + halo into the send buffers
 template <class Real>
 __global__ void __launch_bounds__(256)
-slab_bin_kernel(const Rec<Real>* __restrict__ rec_old, const uint32_t* __restrict__ pid_old, uint32_t own_b_prev, uint32_t t_begin, uint32_t n_own_prev,
-                bool interior, StepConst<Real> k, SlabGeom g,
+slab_bin_kernel(const Rec<Real>* __restrict__ rec_old, const uint32_t* __restrict__ pid_old, uint32_t own_b_prev, uint32_t n_own_prev,
+                StepConst<Real> k, SlabGeom g,
                 uint32_t* __restrict__ cell_count, uint32_t* __restrict__ slot_cell, uint32_t* __restrict__ arrival,
                 void* send_l, void* send_r, SlabDev* __restrict__ sd, DevState* __restrict__ ds) {
     // SORT_ILP inputs per thread, CTA-strided: their loads, then their counting atomics, are in flight together.
     // The owned range is known on the host, so no thread waits for a count from memory first.
-    // Inputs [t_begin, n_own_prev) of the owned range; `interior`: these particles sit at least SLAB_EDGE_COLS columns away
-    // from both ends of the local grid, their launch runs while the halo exchange is already under way, so one of them
-    // that turns out to need sending is an error (it moved more than two cell columns in one sub-step).
-    const uint32_t t0 = t_begin + blockIdx.x * (blockDim.x * SORT_ILP) + threadIdx.x;
+    const uint32_t t0 = blockIdx.x * (blockDim.x * SORT_ILP) + threadIdx.x;
     Rec<Real> r[SORT_ILP];
     uint32_t c[SORT_ILP], a[SORT_ILP];
 #pragma unroll
     for (int j = 0; j < SORT_ILP; ++j) { const uint32_t t = t0 + j * blockDim.x; if (t < n_own_prev) r[j] = ld_rec(rec_old + own_b_prev + t); }
     const bool frozen = ds->flags != 0u;                             // error state: the state stays frozen
-    float vmax = 0.0f;
 #pragma unroll
     for (int j = 0; j < SORT_ILP; ++j) {
         const uint32_t t = t0 + j * blockDim.x;
@@ -191,11 +182,9 @@ slab_bin_kernel(const Rec<Real>* __restrict__ rec_old, const uint32_t* __restric
         if (t >= n_own_prev) continue;
         const uint32_t s = own_b_prev + t;
         if (!frozen) integrate_rec<Real>(r[j], k);
-        vmax = fmaxf(vmax, fmaxf(fabsf((float)r[j].u), fabsf((float)r[j].w)));
         uint32_t gi, gj;
         global_cell<Real>(r[j].x, r[j].y, k, g.gcols, gi, gj);
         if (gi < g.xlo || gi >= g.xhi) atomicOr(&sd->err, SLAB_ERR_MIGRATION);
-        if (interior && ((g.gl && gi <= g.x0) || (g.gr && gi + 1 >= g.x1))) { atomicOr(&sd->err, SLAB_ERR_FAST); continue; }
         if (g.gl && gi <= g.x0) {                                    // migrant (gi < x0) or halo (gi == x0) for the left rank
             const uint32_t q = atomicAdd(&reinterpret_cast<HaloHeader*>(send_l)->count, 1u);
             if (q < g.cap_h) { st_rec(halo_recs<Real>(send_l) + q, r[j]); halo_pids<Real>(send_l, g.cap_h)[q] = pid_old[s]; }
@@ -207,11 +196,6 @@ slab_bin_kernel(const Rec<Real>* __restrict__ rec_old, const uint32_t* __restric
             else atomicOr(&sd->err, SLAB_ERR_HALO);
         }
         if (gi >= g.col_off && gi < g.col_off + g.ncl) c[j] = (gi - g.col_off) * g.rows + gj;   // stays in the local grid (own or ghost column)
-    }
-    {   // the fastest particle of the sub-step: the host uses it to decide whether the next exchange may start early
-        uint32_t vb = __float_as_uint(vmax * 1.0001f);
-        vb = __reduce_max_sync(0xffffffffu, vb);
-        if ((threadIdx.x & 31u) == 0 && vb > sd->vmax_bits) atomicMax(&sd->vmax_bits, vb);
     }
 #pragma unroll
     for (int j = 0; j < SORT_ILP; ++j) if (c[j] != SLAB_INVALID) a[j] = cell_count_fetch_inc(cell_count, c[j]);
@@ -269,9 +253,6 @@ __global__ void slab_counts_kernel(const uint32_t* __restrict__ cell_start, Slab
     sd->c_last2 = cell_start[(ncl >= 2 ? ncl - 2 : 0) * rows];
     sd->c_last1 = cell_start[(ncl >= 1 ? ncl - 1 : 0) * rows];
     sd->n_blocked = g.gl ? sd->c_first2 : 0u;
-    const bool wide = ncl > 2 * SLAB_EDGE_COLS;                  // narrow slabs: every slot is an edge slot
-    sd->c_edge_l = wide ? cell_start[SLAB_EDGE_COLS * rows] : n;
-    sd->c_edge_r = wide ? cell_start[(ncl - SLAB_EDGE_COLS) * rows] : n;
 }
 
 template <class Real>
@@ -421,8 +402,6 @@ struct SlabCollider {
     bool t_acc = false;
     uint64_t substeps_done = 0, launches = 0;
     cudaStream_t own_stream = nullptr, stream = nullptr;
-    cudaStream_t comm_stream = nullptr;              // the M0 exchange runs here, beside the interior bin on `stream`
-    cudaEvent_t ev_edges = nullptr, ev_m0 = nullptr;
     Error err;
 
     int cur = 0;
@@ -509,9 +488,6 @@ struct SlabCollider {
         cfg = c; rank = rank_; nranks = nranks_; device = c.device; n_total = c.count;
         PS_CUDA_TRY(err, cudaStreamCreateWithFlags(&own_stream, cudaStreamNonBlocking));
         stream = own_stream;
-        PS_CUDA_TRY(err, cudaStreamCreateWithFlags(&comm_stream, cudaStreamNonBlocking));
-        PS_CUDA_TRY(err, cudaEventCreateWithFlags(&ev_edges, cudaEventDisableTiming));
-        PS_CUDA_TRY(err, cudaEventCreateWithFlags(&ev_m0, cudaEventDisableTiming));
         g.rows = rows; g.gcols = cols;
         g.x0 = (uint32_t)(((uint64_t)rank * cols) / nranks);
         g.x1 = (uint32_t)(((uint64_t)(rank + 1) * cols) / nranks);
@@ -572,9 +548,6 @@ struct SlabCollider {
 
     void destroy() {
         if (own_stream) cudaStreamSynchronize(own_stream);
-        if (comm_stream) { cudaStreamSynchronize(comm_stream); cudaStreamDestroy(comm_stream); }
-        if (ev_edges) cudaEventDestroy(ev_edges);
-        if (ev_m0) cudaEventDestroy(ev_m0);
         report();
         if (comm) nccl_api().CommDestroy(comm);
         for (auto& r : rec) cudaFree(r);
@@ -608,7 +581,6 @@ struct SlabCollider {
         // slots [0, own_e) are all owned and in arbitrary order; the first sub-step sorts them
         SlabDev h = hc->sd;
         h.own_b = 0; h.n_local = h.own_e;
-        h.c_edge_l = h.c_edge_r = h.own_e;                  // unsorted: every slot may hold a boundary particle
         PS_CUDA_TRY(err, cudaMemcpyAsync(sd, &h, sizeof(SlabDev), cudaMemcpyHostToDevice, stream));
         PS_CUDA_TRY(err, cudaStreamSynchronize(stream));
         last = h;
@@ -675,7 +647,6 @@ struct SlabCollider {
         const uint32_t e = hc->sd.err;
         if (e & SLAB_ERR_PROTOCOL) return fail(PS_ERR_NCCL, "boundary hand-over sizes disagree between neighbouring ranks");
         if (e & SLAB_ERR_MIGRATION) return fail(PS_ERR_MIGRATION, "a particle crossed a whole neighbouring slab in one sub-step");
-        if (e & SLAB_ERR_FAST) return fail(PS_ERR_MIGRATION, "a particle moved more than two cell columns in one sub-step and reached a slab boundary (slab scenes need sub-step displacements below two cells)");
         if (e & SLAB_ERR_HALO) return fail(PS_ERR_CAPACITY, "halo / migration buffer too small for this scene");
         if (e & SLAB_ERR_CAPACITY) return fail(PS_ERR_CAPACITY, "this rank's slab holds more particles than it was sized for");
         if (hc->ds.flags & FLAG_CORRUPT) return fail(PS_ERR_CUDA, "rank " + std::to_string(rank) + ": slot " + std::to_string(hc->ds.dbg[0]) + " of " + std::to_string(hc->ds.dbg[3]) +
@@ -698,48 +669,18 @@ struct SlabCollider {
     uint32_t own_b_step = 0, n_own_step = 0;
     size_t halo_msg_bytes() const { return halo_bytes<Real>(g.cap_h); }
 
-    // stage 1: integrate + bin own particles; send_l / send_r hold the M0 messages once the EDGE slots are done.
-    // The owned slots are in cell order, so the particles that can reach a neighbour's columns or this rank's boundary
-    // columns within one sub-step are two short slot ranges at the ends (SLAB_EDGE_COLS columns each).  They are binned
-    // first; the exchange then runs beside the binning of everything else (substep()).
-    uint32_t edge_l_step = 0, edge_r_step = 0;
-    void launch_bin(uint32_t t_begin, uint32_t t_end, bool interior) {
-        if (t_end <= t_begin) return;
-        const uint32_t m = t_end - t_begin;
-        slab_bin_kernel<Real><<<(m + 256 * SORT_ILP - 1) / (256 * SORT_ILP), 256, 0, stream>>>(rec[cur], pid[cur], own_b_step, t_begin, t_end, interior, k_step, g,
-                                                                                             cell_count, slot_cell, arrival, send_l, send_r, sd, ds);
-        ++launches;
-    }
-    int stage_bin_edges() {
+    // stage 1: integrate + bin own particles; send_l / send_r now hold the M0 messages
+    int stage_bin() {
         if (err.status != PS_OK) return err.status;
         k_step = consts();
         cudaStream_t st = stream;
         PS_CUDA_TRY(err, cudaMemsetAsync(cell_count, 0, cell_count_bytes(ncell_local), st));
         slab_begin_kernel<Real><<<1, 32, 0, st>>>(sd, ds, send_l, send_r);
-        ++launches;
         own_b_step = last.own_b; n_own_step = last.own_e - last.own_b;   // the layout left by the previous sub-step (host copy)
-        edge_l_step = last.c_edge_l < n_own_step ? last.c_edge_l : n_own_step;
-        edge_r_step = last.c_edge_r < n_own_step ? last.c_edge_r : n_own_step;
-        if (edge_r_step < edge_l_step) edge_r_step = edge_l_step;
-        // The split assumes that nobody further than two cell columns from a boundary reaches it within this sub-step.  The
-        // fastest particle of the previous sub-step says how far anybody travelled then (collisions can add to that, hence
-        // the factor two); violent scenes, and the first sub-step, treat every slot as an edge slot.
-        float vmax_prev; std::memcpy(&vmax_prev, &last.vmax_bits, sizeof(float));
-        const double reach = 2.0 * (double)vmax_prev * (double)k_step.dt;
-        if (substeps_done == 0 || !(reach < 2.0 * cfg.grid_size)) edge_l_step = edge_r_step = n_own_step;
-        launch_bin(0u, edge_l_step, false);
-        launch_bin(edge_r_step, n_own_step, false);
+        slab_bin_kernel<Real><<<(n_own_step + 256 * SORT_ILP - 1) / (256 * SORT_ILP) + 1, 256, 0, st>>>(rec[cur], pid[cur], own_b_step, n_own_step, k_step, g, cell_count, slot_cell, arrival, send_l, send_r, sd, ds);
+        launches += 2;
         PS_CUDA_TRY(err, cudaGetLastError());
         return PS_OK;
-    }
-    int stage_bin_interior() {
-        launch_bin(edge_l_step, edge_r_step, true);
-        PS_CUDA_TRY(err, cudaGetLastError());
-        return PS_OK;
-    }
-    int stage_bin() {
-        const int rc = stage_bin_edges();
-        return rc ? rc : stage_bin_interior();
     }
 
     // stage 2 (recv_l / recv_r hold the neighbours' M0): local sort, detect, phase A, one host synchronisation
@@ -816,19 +757,14 @@ struct SlabCollider {
         cudaStream_t st = stream;
         int rc;
         tick(0);
-        if ((rc = stage_bin_edges())) return rc;
-        if (nranks > 1) {                                                         // ---- M0: migrants + halo, both ways, beside the interior bin
-            PS_CUDA_TRY(err, cudaEventRecord(ev_edges, st));
-            PS_CUDA_TRY(err, cudaStreamWaitEvent(comm_stream, ev_edges, 0));
-            if ((rc = nccl_try(api.GroupStart(), "ncclGroupStart"))) return rc;
-            if (g.gl) { api.Send(send_l, hb, kNcclUint8, rank - 1, comm, comm_stream); api.Recv(recv_l, hb, kNcclUint8, rank - 1, comm, comm_stream); }
-            if (g.gr) { api.Send(send_r, hb, kNcclUint8, rank + 1, comm, comm_stream); api.Recv(recv_r, hb, kNcclUint8, rank + 1, comm, comm_stream); }
-            if ((rc = nccl_try(api.GroupEnd(), "ncclGroupEnd (M0)"))) return rc;
-            PS_CUDA_TRY(err, cudaEventRecord(ev_m0, comm_stream));
-        }
-        if ((rc = stage_bin_interior())) return rc;
+        if ((rc = stage_bin())) return rc;
         tick(1);
-        if (nranks > 1) PS_CUDA_TRY(err, cudaStreamWaitEvent(st, ev_m0, 0));
+        if (nranks > 1) {                                                         // ---- M0: migrants + halo, both ways
+            if ((rc = nccl_try(api.GroupStart(), "ncclGroupStart"))) return rc;
+            if (g.gl) { api.Send(send_l, hb, kNcclUint8, rank - 1, comm, st); api.Recv(recv_l, hb, kNcclUint8, rank - 1, comm, st); }
+            if (g.gr) { api.Send(send_r, hb, kNcclUint8, rank + 1, comm, st); api.Recv(recv_r, hb, kNcclUint8, rank + 1, comm, st); }
+            if ((rc = nccl_try(api.GroupEnd(), "ncclGroupEnd (M0)"))) return rc;
+        }
         tick(2);
         if ((rc = stage_build())) return rc;
         tick(5);
