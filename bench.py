@@ -9,8 +9,15 @@ Workload (BASELINE.json configs[2], the configuration the roofline metric is quo
     64 Mi particles per GPU, integrate + wall bounce, fp32 SoA, reference scene constants.
     A "step" is one Solver.updatePhysics frame = sub_steps (8) passes of the hot kernel, one launch each.
     N > 1: every rank owns its own 64 Mi-particle index shard (no data-path collective) -> weak scaling.
-"value" is timed with the state resident in HBM; "e2e" is the same frame driven through the C ABI
-from pinned HOST buffers laid out like core.zig's []@Vector(2,f64), H2D and D2H inside the timed region.
+"value" is timed with the state resident in HBM (fp32; roofline.f64 = the f64 build); "e2e" is the same frame driven through
+the C ABI from pinned HOST buffers laid out like core.zig's []@Vector(2,f64), on an f64 handle, H2D and D2H inside the timed
+region (e2e.f32_host_f32_device: the fp32 pair; e2e.resident_pos_f32: state resident, positions read back as f32).
+
+Every run also times the collision-bearing configurations and reports them under config.collide_* (headline numbers) and in
+the trailing "collide" object (everything): BASELINE.json configs[4], ONE 256 Mi-particle collision scene on all N GPUs (the
+single-GPU handle at N = 1; x-slabs over NCCL send/recv at N > 1, strong scaling, with the per-stage breakdown and a 1 Mi-particle
+run through the same NCCL path compared with the CPU oracle bit for bit - the run fails if it differs); at N = 1 also
+configs[3] (16 Mi particles) and main.zig's default scene as a settled pile under gravity against the CPU port.
 """
 from __future__ import annotations
 
