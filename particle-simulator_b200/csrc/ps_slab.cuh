@@ -59,8 +59,9 @@ struct SlabDev {               // device-side counters, copied to the host once 
     uint32_t err;
     uint32_t n_own_prev;       // owned particles at the start of this sub-step
     uint32_t zero;             // always 0 (range start for the pack / unpack kernels)
+    uint32_t one;              // always 1
     uint32_t own_b_prev;       // first owned slot of the layout this sub-step started from
-    uint32_t pad[3];
+    uint32_t pad[2];
 };
 
 // halo / migration message: header + records + particle indices
@@ -378,6 +379,48 @@ slab_unpack_kernel(void* buf, Rec<Real>* __restrict__ rec, const uint32_t* __res
     if (i < n && i < cap_h) st_rec(rec + first + i, ld_rec(halo_recs<Real>(buf) + i));
 }
 
+// ---- one-sided transport between x-neighbours (processes of one box, peer memory over NVLink) ----------------------
+// A message is pushed straight into the neighbour's receive buffer (mapped with cudaIpcOpenMemHandle) by plain stores,
+// followed by a system-wide fence and a sequence number in the neighbour's flag word; the neighbour's stream holds a
+// one-warp kernel that waits for that number.  An exchange costs a few microseconds instead of the tens an
+// ncclSend / ncclRecv pair takes, and it sits on the neighbour-to-neighbour critical cycle of every sub-step twice.
+// `gate` (optional): send only if (*gate != 0) == gate_want — the boundary hand-over is queued twice, after phase A and
+// after phase B, and the device decides which of the two carries it (no host round trip).
+template <class Real>
+__global__ void __launch_bounds__(1024)
+slab_push_kernel(const void* __restrict__ src0, void* dst0, const void* __restrict__ src1, void* dst1, uint32_t cap_h,
+                 uint32_t* flag0, uint32_t* flag1, uint32_t seq, const uint32_t* gate, uint32_t gate_want) {
+    const void* src = blockIdx.x ? src1 : src0;
+    void* dst = blockIdx.x ? dst1 : dst0;
+    uint32_t* flag = blockIdx.x ? flag1 : flag0;
+    if (!dst) return;
+    if (gate && ((*gate != 0u) ? 1u : 0u) != gate_want) return;
+    const uint32_t count = min(reinterpret_cast<const HaloHeader*>(src)->count, cap_h);
+    const uint4* s4 = reinterpret_cast<const uint4*>(src);
+    uint4* d4 = reinterpret_cast<uint4*>(dst);
+    const uint32_t rec_v = (uint32_t)((sizeof(HaloHeader) + (size_t)count * sizeof(Rec<Real>)) / 16);       // header + records, in 16-byte units
+    for (uint32_t i = threadIdx.x; i < rec_v; i += blockDim.x) d4[i] = s4[i];
+    const size_t pid_off = (sizeof(HaloHeader) + (size_t)cap_h * sizeof(Rec<Real>)) / 16;                   // particle indices (slab_export needs them for M0)
+    const uint32_t pid_v = (count + 3u) / 4u;
+    for (uint32_t i = threadIdx.x; i < pid_v; i += blockDim.x) d4[pid_off + i] = s4[pid_off + i];
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) { *reinterpret_cast<volatile uint32_t*>(flag) = seq; __threadfence_system(); }
+}
+
+// waits until the flag words hold `seq` (the neighbours' pushes of this sub-step have landed); gives up after ~20 s so that a
+// dead neighbour turns into an error status instead of a kernel that never ends
+__global__ void slab_wait_kernel(const uint32_t* flag0, const uint32_t* flag1, uint32_t seq, SlabDev* __restrict__ sd) {
+    const uint32_t* flag = threadIdx.x == 0 ? flag0 : (threadIdx.x == 1 ? flag1 : nullptr);
+    if (!flag) return;
+    const unsigned long long t0 = global_ns();
+    while (*reinterpret_cast<const volatile uint32_t*>(flag) != seq) {
+        __nanosleep(200);
+        if (global_ns() - t0 > 20000000000ull) { atomicOr(&sd->err, SLAB_ERR_PROTOCOL); return; }
+    }
+    __threadfence_system();
+}
+
 template <class Real>
 __global__ void __launch_bounds__(256)
 slab_export_kernel(const Rec<Real>* __restrict__ rec, const uint32_t* __restrict__ pid, uint32_t first, uint32_t count,
@@ -414,6 +457,15 @@ struct SlabCollider {
     unsigned long long* head = nullptr;
     uint2* wl[3] = {nullptr, nullptr, nullptr};
     void *send_l = nullptr, *send_r = nullptr, *recv_l = nullptr, *recv_r = nullptr;
+    void *in_l = nullptr, *in_r = nullptr, *in_m1 = nullptr;      // where this sub-step's M0 (from the left / right) and M1 have arrived
+    // one-sided transport (see slab_push_kernel): my receive block, and the neighbours' blocks mapped into this process
+    char* xbuf = nullptr; char *x_left = nullptr, *x_right = nullptr;
+    bool p2p_l = false, p2p_r = false;
+    size_t x_slot = 0;                                            // bytes per message buffer inside a receive block
+    static constexpr size_t kFlagBytes = 1024;                    // six flag words, 128 bytes apart
+    enum { X_M0_FROM_LEFT = 0, X_M0_FROM_RIGHT = 2, X_M1 = 4 };   // buffer / flag index = kind + parity of the sub-step
+    uint32_t* x_flag(char* base, int idx) const { return reinterpret_cast<uint32_t*>(base + 128 * idx); }
+    void* x_msg(char* base, int idx) const { return base + kFlagBytes + x_slot * idx; }
     DevState* ds = nullptr;
     SlabDev* sd = nullptr;
     struct HostCopy { SlabDev sd; DevState ds; };
@@ -522,7 +574,7 @@ struct SlabCollider {
         if ((rc = alloc(&chunks, (uint64_t)LIST_CHUNK * cap))) return rc;
         PS_CUDA_TRY(err, cudaMemsetAsync(head, 0, cap * sizeof(unsigned long long), stream));
         for (int i = 0; i < 3; ++i) if ((rc = alloc(&wl[i], cap))) return rc;
-        const size_t hb = halo_bytes<Real>(g.cap_h);
+        const size_t hb = round_up(halo_bytes<Real>(g.cap_h), 256);     // (the push kernel copies whole 16-byte units)
         PS_CUDA_TRY(err, cudaMalloc(&send_l, hb)); PS_CUDA_TRY(err, cudaMalloc(&send_r, hb));
         PS_CUDA_TRY(err, cudaMalloc(&recv_l, hb)); PS_CUDA_TRY(err, cudaMalloc(&recv_r, hb));
         PS_CUDA_TRY(err, cudaMemsetAsync(send_l, 0, hb, stream)); PS_CUDA_TRY(err, cudaMemsetAsync(send_r, 0, hb, stream));
@@ -537,17 +589,67 @@ struct SlabCollider {
         PS_CUDA_TRY(err, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, resolve_kernel<Real>, RESOLVE_THREADS, 0));
         PS_CUDA_TRY(err, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
         resolve_grid = per_sm * sms;
+        in_l = recv_l; in_r = recv_r; in_m1 = recv_l;
         if (nranks > 1 && id) {                // id == NULL: ranks emulated in one process (SlabGroupLocal), no communicator
             const NcclApi& api = nccl_api();
             if (!api.ok) return fail(PS_ERR_NCCL, api.error);
             if ((rc = nccl_try(api.CommInitRank(&comm, nranks, *id, rank), "ncclCommInitRank"))) return rc;
+            if ((rc = setup_peer_transport(hb))) return rc;
         }
         PS_CUDA_TRY(err, cudaStreamSynchronize(stream));
         return PS_OK;
     }
 
+    // One-sided transport between x-neighbours: every rank allocates one receive block (flags + six message buffers), hands its
+    // IPC handle to both neighbours over the communicator it already has, and maps theirs.  A boundary uses the one-sided path
+    // only if BOTH of its ranks managed to map each other (they tell each other); otherwise it stays on ncclSend / ncclRecv.
+    // PS_SLAB_TRANSPORT=nccl keeps every boundary on NCCL (set it on all ranks).
+    int setup_peer_transport(size_t hb) {
+        const char* want = getenv("PS_SLAB_TRANSPORT");
+        const bool try_p2p = !(want && std::string(want) == "nccl");
+        const NcclApi& api = nccl_api();
+        x_slot = hb;
+        struct Hello { cudaIpcMemHandle_t handle; uint32_t ok; uint32_t pad[3]; };
+        Hello mine{}; Hello* dev = nullptr;
+        if (try_p2p && cudaMalloc((void**)&xbuf, kFlagBytes + 6 * x_slot) == cudaSuccess) {
+            PS_CUDA_TRY(err, cudaMemsetAsync(xbuf, 0, kFlagBytes + 6 * x_slot, stream));
+            mine.ok = cudaIpcGetMemHandle(&mine.handle, xbuf) == cudaSuccess ? 1u : 0u;
+        }
+        cudaGetLastError();
+        // round 1: handles; round 2: "I mapped yours"
+        PS_CUDA_TRY(err, cudaMalloc((void**)&dev, 3 * sizeof(Hello)));                    // [0] mine, [1] from left, [2] from right
+        Hello got[3]{};
+        for (int round = 0; round < 2; ++round) {
+            PS_CUDA_TRY(err, cudaMemcpyAsync(dev, &mine, sizeof(Hello), cudaMemcpyHostToDevice, stream));
+            int rc;
+            if ((rc = nccl_try(api.GroupStart(), "ncclGroupStart"))) return rc;
+            if (g.gl) { api.Send(dev, sizeof(Hello), kNcclUint8, rank - 1, comm, stream); api.Recv(dev + 1, sizeof(Hello), kNcclUint8, rank - 1, comm, stream); }
+            if (g.gr) { api.Send(dev, sizeof(Hello), kNcclUint8, rank + 1, comm, stream); api.Recv(dev + 2, sizeof(Hello), kNcclUint8, rank + 1, comm, stream); }
+            if ((rc = nccl_try(api.GroupEnd(), "ncclGroupEnd (transport set-up)"))) return rc;
+            PS_CUDA_TRY(err, cudaMemcpyAsync(got, dev, 3 * sizeof(Hello), cudaMemcpyDeviceToHost, stream));
+            PS_CUDA_TRY(err, cudaStreamSynchronize(stream));
+            if (round == 0) {
+                // map the neighbours' blocks; `mine.ok` now carries, per side, whether that worked (bit 0 left, bit 1 right)
+                uint32_t mapped = 0;
+                if (g.gl && mine.ok && got[1].ok && cudaIpcOpenMemHandle((void**)&x_left, got[1].handle, cudaIpcMemLazyEnablePeerAccess) == cudaSuccess) mapped |= 1u;
+                if (g.gr && mine.ok && got[2].ok && cudaIpcOpenMemHandle((void**)&x_right, got[2].handle, cudaIpcMemLazyEnablePeerAccess) == cudaSuccess) mapped |= 2u;
+                cudaGetLastError();
+                mine.ok = mapped;
+            } else {
+                p2p_l = g.gl && (mine.ok & 1u) && (got[1].ok & 2u);     // I mapped the left rank's block and it mapped mine (its right side)
+                p2p_r = g.gr && (mine.ok & 2u) && (got[2].ok & 1u);
+            }
+        }
+        cudaFree(dev);
+        if (getenv("PS_SLAB_VERBOSE")) fprintf(stderr, "[slab] rank %d transport: left %s, right %s\n", rank, g.gl ? (p2p_l ? "peer stores" : "nccl") : "-", g.gr ? (p2p_r ? "peer stores" : "nccl") : "-");
+        return PS_OK;
+    }
+
     void destroy() {
         if (own_stream) cudaStreamSynchronize(own_stream);
+        if (x_left) cudaIpcCloseMemHandle(x_left);
+        if (x_right) cudaIpcCloseMemHandle(x_right);
+        cudaFree(xbuf);
         report();
         if (comm) nccl_api().CommDestroy(comm);
         for (auto& r : rec) cudaFree(r);
@@ -580,7 +682,7 @@ struct SlabCollider {
         if (hc->sd.err & SLAB_ERR_CAPACITY) return fail(PS_ERR_CAPACITY, "this rank's slab holds more particles than it was sized for");
         // slots [0, own_e) are all owned and in arbitrary order; the first sub-step sorts them
         SlabDev h = hc->sd;
-        h.own_b = 0; h.n_local = h.own_e;
+        h.own_b = 0; h.n_local = h.own_e; h.one = 1u;
         PS_CUDA_TRY(err, cudaMemcpyAsync(sd, &h, sizeof(SlabDev), cudaMemcpyHostToDevice, stream));
         PS_CUDA_TRY(err, cudaStreamSynchronize(stream));
         last = h;
@@ -686,19 +788,19 @@ struct SlabCollider {
     // stage 2 (recv_l / recv_r hold the neighbours' M0): local sort, detect, phase A, one host synchronisation
     int stage_build() {
         const int nw = cur ^ 1;
-        const unsigned g_cap = (g.cap + 255) / 256, g_in = (n_own_step + 2 * g.cap_h + 256 * SORT_ILP - 1) / (256 * SORT_ILP), g_h = (2 * g.cap_h + 255) / 256;
+        const unsigned g_in = (n_own_step + 2 * g.cap_h + 256 * SORT_ILP - 1) / (256 * SORT_ILP), g_h = (2 * g.cap_h + 255) / 256;
         cudaStream_t st = stream;
         const StepConst<Real>& k = k_step;
         if (int d = dbg("bin")) return d;
-        slab_bin_recv_kernel<Real><<<g_h, 256, 0, st>>>(recv_l, recv_r, k, g, cell_count, slot_cell, arrival, sd, ds);
+        slab_bin_recv_kernel<Real><<<g_h, 256, 0, st>>>(in_l, in_r, k, g, cell_count, slot_cell, arrival, sd, ds);
         if (int d = dbg("bin_recv")) return d;
         PS_CUDA_TRY(err, exclusive_scan<uint8_t>(reinterpret_cast<const uint8_t*>(cell_count), cell_start, ncell_local, scan_sums, cell_start + ncell_local, &ds->max_cell, st));
         if (int d = dbg("scan")) return d;
         slab_counts_kernel<<<1, 32, 0, st>>>(cell_start, g, sd);
         if (int d = dbg("counts")) return d;
-        slab_place_kernel<Real><<<g_in, 256, 0, st>>>(slot_cell, arrival, pid[cur], own_b_step, n_own_step, cell_start, g, recv_l, recv_r, tmp_id);
+        slab_place_kernel<Real><<<g_in, 256, 0, st>>>(slot_cell, arrival, pid[cur], own_b_step, n_own_step, cell_start, g, in_l, in_r, tmp_id);
         if (int d = dbg("place")) return d;
-        slab_move_kernel<Real><<<g_in, 256, 0, st>>>(rec[cur], pid[cur], own_b_step, n_own_step, slot_cell, cell_start, tmp_id, k, g, recv_l, recv_r, ds, rec[nw], pid[nw]);
+        slab_move_kernel<Real><<<g_in, 256, 0, st>>>(rec[cur], pid[cur], own_b_step, n_own_step, slot_cell, cell_start, tmp_id, k, g, in_l, in_r, ds, rec[nw], pid[nw]);
         if (int d = dbg("move")) return d;
         SlabView sv{g.gl, g.gr, g.ncl, g.col_off, g.gcols, &sd->n_local, &sd->n_blocked, brem};
         const uint64_t n_hi = (uint64_t)n_own_step + 2ull * g.cap_h;             // at most this many local slots after the exchange
@@ -733,7 +835,7 @@ struct SlabCollider {
     // stage 3 (recv_l holds the left rank's M1): take over the boundary states, unblock, phase B
     int stage_phase_b() {
         cudaStream_t st = stream;
-        slab_unpack_kernel<Real><<<(g.cap_h + 255) / 256, 256, 0, st>>>(recv_l, rec[cur ^ 1], &sd->zero, &sd->c_first2, g.cap_h, sd);
+        slab_unpack_kernel<Real><<<(g.cap_h + 255) / 256, 256, 0, st>>>(in_m1, rec[cur ^ 1], &sd->zero, &sd->c_first2, g.cap_h, sd);
         slab_unblock_kernel<<<(h_step.c_first2 + 255) / 256 + 1, 256, 0, st>>>(head, brem, wl[r0_step % 3], &ds->wl_count[r0_step % 3], r0_step, sd);
         launches += 2;
         if (int d = dbg("unpack+unblock")) return d;
@@ -750,36 +852,71 @@ struct SlabCollider {
         return PS_OK;
     }
 
-    // One process per GPU: the stages above with NCCL send / recv between x-neighbours.
+    int push(const void* src0, void* dst0, uint32_t* flag0, const void* src1, void* dst1, uint32_t* flag1, uint32_t seq, const uint32_t* gate, uint32_t gate_want) {
+        slab_push_kernel<Real><<<2, 1024, 0, stream>>>(src0, dst0, src1, dst1, g.cap_h, flag0, flag1, seq, gate, gate_want);
+        ++launches;
+        PS_CUDA_TRY(err, cudaGetLastError());
+        return PS_OK;
+    }
+
+    // One process per GPU: the stages above with the exchanges between x-neighbours — one-sided stores into the neighbour's
+    // receive block where both sides could map each other (the usual case on one NVSwitch box), ncclSend / ncclRecv otherwise.
     int substep() {
         const NcclApi& api = nccl_api();
         const size_t hb = halo_msg_bytes();
         cudaStream_t st = stream;
+        const uint32_t seq = (uint32_t)(substeps_done + 1);
+        const int par = (int)(seq & 1u);
         int rc;
         tick(0);
         if ((rc = stage_bin())) return rc;
         tick(1);
         if (nranks > 1) {                                                         // ---- M0: migrants + halo, both ways
-            if ((rc = nccl_try(api.GroupStart(), "ncclGroupStart"))) return rc;
-            if (g.gl) { api.Send(send_l, hb, kNcclUint8, rank - 1, comm, st); api.Recv(recv_l, hb, kNcclUint8, rank - 1, comm, st); }
-            if (g.gr) { api.Send(send_r, hb, kNcclUint8, rank + 1, comm, st); api.Recv(recv_r, hb, kNcclUint8, rank + 1, comm, st); }
-            if ((rc = nccl_try(api.GroupEnd(), "ncclGroupEnd (M0)"))) return rc;
+            if (p2p_l || p2p_r) {
+                if ((rc = push(send_l, p2p_l ? x_msg(x_left, X_M0_FROM_RIGHT + par) : nullptr, p2p_l ? x_flag(x_left, X_M0_FROM_RIGHT + par) : nullptr,
+                               send_r, p2p_r ? x_msg(x_right, X_M0_FROM_LEFT + par) : nullptr, p2p_r ? x_flag(x_right, X_M0_FROM_LEFT + par) : nullptr,
+                               seq, nullptr, 0u))) return rc;
+            }
+            if ((g.gl && !p2p_l) || (g.gr && !p2p_r)) {
+                if ((rc = nccl_try(api.GroupStart(), "ncclGroupStart"))) return rc;
+                if (g.gl && !p2p_l) { api.Send(send_l, hb, kNcclUint8, rank - 1, comm, st); api.Recv(recv_l, hb, kNcclUint8, rank - 1, comm, st); }
+                if (g.gr && !p2p_r) { api.Send(send_r, hb, kNcclUint8, rank + 1, comm, st); api.Recv(recv_r, hb, kNcclUint8, rank + 1, comm, st); }
+                if ((rc = nccl_try(api.GroupEnd(), "ncclGroupEnd (M0)"))) return rc;
+            }
+            if (p2p_l || p2p_r) {
+                slab_wait_kernel<<<1, 32, 0, st>>>(p2p_l ? x_flag(xbuf, X_M0_FROM_LEFT + par) : nullptr, p2p_r ? x_flag(xbuf, X_M0_FROM_RIGHT + par) : nullptr, seq, sd);
+                ++launches;
+            }
+            in_l = p2p_l ? x_msg(xbuf, X_M0_FROM_LEFT + par) : recv_l;
+            in_r = p2p_r ? x_msg(xbuf, X_M0_FROM_RIGHT + par) : recv_r;
         }
         tick(2);
         if ((rc = stage_build())) return rc;
         tick(5);
         const bool send_now = send_now_step;
-        if (send_now && (rc = pack_m1())) return rc;
-        if (nranks > 1) {                                                         // ---- M1: boundary states to the right
+        if (g.gr && p2p_r) {
+            // hand-over to the right, queued twice (here and after phase B); the device sends the one that applies
+            if ((rc = pack_m1())) return rc;
+            if ((rc = push(send_r, x_msg(x_right, X_M1 + par), x_flag(x_right, X_M1 + par), nullptr, nullptr, nullptr, seq, force_late ? &sd->one : &sd->right_incomplete, 0u))) return rc;
+        } else if (send_now && (rc = pack_m1())) return rc;
+        if (nranks > 1 && ((g.gr && !p2p_r && send_now) || (g.gl && !p2p_l))) {     // ---- M1: boundary states to the right
             if ((rc = nccl_try(api.GroupStart(), "ncclGroupStart"))) return rc;
-            if (send_now) api.Send(send_r, hb, kNcclUint8, rank + 1, comm, st);
-            if (g.gl) api.Recv(recv_l, hb, kNcclUint8, rank - 1, comm, st);
+            if (g.gr && !p2p_r && send_now) api.Send(send_r, hb, kNcclUint8, rank + 1, comm, st);
+            if (g.gl && !p2p_l) api.Recv(recv_l, hb, kNcclUint8, rank - 1, comm, st);
             if ((rc = nccl_try(api.GroupEnd(), "ncclGroupEnd (M1)"))) return rc;
         }
+        if (g.gl && p2p_l) {
+            slab_wait_kernel<<<1, 32, 0, st>>>(x_flag(xbuf, X_M1 + par), nullptr, seq, sd);
+            ++launches;
+        }
+        in_m1 = p2p_l ? x_msg(xbuf, X_M1 + par) : recv_l;
         tick(6);
         if (g.gl && (rc = stage_phase_b())) return rc;
         tick(7);
-        if (g.gr && !send_now) {                                                  // rare: our right boundary depended on the left one
+        if (g.gr && p2p_r) {
+            if ((rc = pack_m1())) return rc;
+            if ((rc = push(send_r, x_msg(x_right, X_M1 + par), x_flag(x_right, X_M1 + par), nullptr, nullptr, nullptr, seq, force_late ? &sd->one : &sd->right_incomplete, 1u))) return rc;
+        } else if (g.gr && !send_now) {                                           // rare: our right boundary depended on the left one
             if ((rc = pack_m1())) return rc;
             if ((rc = nccl_try(api.Send(send_r, hb, kNcclUint8, rank + 1, comm, st), "ncclSend (late M1)"))) return rc;
         }
@@ -788,7 +925,6 @@ struct SlabCollider {
         tock();
         return rc;
     }
-
 
     // Waits for everything queued and reports what the LAST sub-step raised after its one mid-step read-back (phase B's
     // resolve, a late hand-over): without this a failed final sub-step would look like success.
