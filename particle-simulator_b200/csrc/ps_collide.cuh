@@ -736,6 +736,7 @@ __device__ __forceinline__ void ps_keep(double x) { asm volatile("" :: "d"(x)); 
 #define PS_KEEP(x) do {} while (0)
 #endif
 
+constexpr uint32_t RESOLVE_CONTINUE = 0xffffffffu;
 constexpr int RESOLVE_THREADS = 1024;     // one CTA per SM in the grid phase: the grid barrier has 148 participants
 constexpr int RESOLVE_TAIL_THREADS = 256; // the single-CTA tail keeps 8 warps (a CTA barrier among 32 warps is slower)
 constexpr uint32_t RESOLVE_TAIL = 512;    // work lists this short are finished by one CTA out of shared memory (deep chains: hundreds of short rounds)
@@ -880,7 +881,10 @@ resolve_kernel(Rec<Real>* rec, const uint32_t* __restrict__ chunks, const uint32
         if (leader) ds->wl_count[0] = 0;
         return;
     }
-    uint32_t r = r_start;                                    // > 0 only for the second phase of a slab sub-step (ps_slab.cuh)
+    // r_start > 0 only for the second phase of a slab sub-step (ps_slab.cuh); RESOLVE_CONTINUE = "the round after the last one
+    // of the previous launch", read on the device so that the host need not know it
+    uint32_t r = r_start == RESOLVE_CONTINUE ? ds->rounds_last + 1u : r_start;
+    const uint32_t r_begin = r;
     const bool trace = leader && ds->trace_on && r_start == 0;
     const unsigned long long t_begin = trace ? global_ns() : 0ull;
     // grid phase: long work lists, one grid barrier per round
@@ -976,7 +980,7 @@ resolve_kernel(Rec<Real>* rec, const uint32_t* __restrict__ chunks, const uint32
         if (left != 0) atomicOr(&ds->flags, FLAG_CAPACITY);          // ran out of round stamps (never in practice)
         ds->rounds_last = r;
         if (trace) ds->trace_rounds = r < 63 ? r + 1 : 64;
-        ds->rounds_total += r - r_start;
+        ds->rounds_total += r - r_begin;
         if (r_start == 0) {
             ds->inc_total = ds->entries_used;
             ds->pairs_total += ds->entries_used / 2;

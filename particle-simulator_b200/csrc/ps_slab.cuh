@@ -341,16 +341,20 @@ slab_right_check_kernel(const unsigned long long* __restrict__ head, const uint3
 }
 
 // M1 has been received into the records of the first two local columns: make their sub-lists visible
+// (r0 = RESOLVE_CONTINUE: the round after phase A's last one, read from the device)
 __global__ void __launch_bounds__(256)
-slab_unblock_kernel(unsigned long long* __restrict__ head, uint32_t* __restrict__ brem, uint2* __restrict__ wl, uint32_t* __restrict__ wl_count,
+slab_unblock_kernel(unsigned long long* __restrict__ head, uint32_t* __restrict__ brem, uint2* wl0, uint2* wl1, uint2* wl2, DevState* __restrict__ ds,
                     uint32_t r0, const SlabDev* __restrict__ sd) {
     const uint32_t a = blockIdx.x * blockDim.x + threadIdx.x;
     if (a >= sd->n_blocked) return;
     if (!brem[a]) return;
     brem[a] = 0u;
+    if (r0 == RESOLVE_CONTINUE) r0 = ds->rounds_last + 1u;
+    const uint32_t li = r0 % 3u;
+    uint2* wl = li == 0u ? wl0 : (li == 1u ? wl1 : wl2);
     const uint32_t e = head_low(head[a]) | HEAD_LIVE;            // entry 0 as detect left it, now visible
     head[a] = head_word(r0, 0u, e);                              // stamp r0 = "on the work list of round r0"
-    wl[atomicAdd(wl_count, 1u)] = make_uint2(a, e);
+    wl[atomicAdd(&ds->wl_count[li], 1u)] = make_uint2(a, e);
 }
 
 // boundary hand-over (M1): a contiguous range of records with its length in front; fixed-size messages,
@@ -445,6 +449,7 @@ struct SlabCollider {
     bool t_acc = false;
     uint64_t substeps_done = 0, launches = 0;
     cudaStream_t own_stream = nullptr, stream = nullptr;
+    cudaEvent_t ev_rb = nullptr;                     // the mid-step copies of the device counters have landed
     Error err;
 
     int cur = 0;
@@ -540,6 +545,7 @@ struct SlabCollider {
         cfg = c; rank = rank_; nranks = nranks_; device = c.device; n_total = c.count;
         PS_CUDA_TRY(err, cudaStreamCreateWithFlags(&own_stream, cudaStreamNonBlocking));
         stream = own_stream;
+        PS_CUDA_TRY(err, cudaEventCreateWithFlags(&ev_rb, cudaEventDisableTiming));
         g.rows = rows; g.gcols = cols;
         g.x0 = (uint32_t)(((uint64_t)rank * cols) / nranks);
         g.x1 = (uint32_t)(((uint64_t)(rank + 1) * cols) / nranks);
@@ -650,6 +656,7 @@ struct SlabCollider {
         if (x_left) cudaIpcCloseMemHandle(x_left);
         if (x_right) cudaIpcCloseMemHandle(x_right);
         cudaFree(xbuf);
+        if (ev_rb) cudaEventDestroy(ev_rb);
         report();
         if (comm) nccl_api().CommDestroy(comm);
         for (auto& r : rec) cudaFree(r);
@@ -787,6 +794,10 @@ struct SlabCollider {
 
     // stage 2 (recv_l / recv_r hold the neighbours' M0): local sort, detect, phase A, one host synchronisation
     int stage_build() {
+        const int rc = stage_build_queue();
+        return rc ? rc : stage_build_wait();
+    }
+    int stage_build_queue() {
         const int nw = cur ^ 1;
         const unsigned g_in = (n_own_step + 2 * g.cap_h + 256 * SORT_ILP - 1) / (256 * SORT_ILP), g_h = (2 * g.cap_h + 255) / 256;
         cudaStream_t st = stream;
@@ -815,7 +826,16 @@ struct SlabCollider {
         if (int d = dbg("resolve A")) return d;
         if (g.gr) { slab_right_check_kernel<<<(2 * g.cap_h + 255) / 256, 256, 0, st>>>(head, brem, sd); ++launches; }   // two columns of slots at most
         tick(4);
-        if ((rc = read_back())) return rc;                                        // the one host synchronisation of the sub-step
+        PS_CUDA_TRY(err, cudaMemcpyAsync(&hc->sd, sd, sizeof(SlabDev), cudaMemcpyDeviceToHost, stream));
+        PS_CUDA_TRY(err, cudaMemcpyAsync(&hc->ds, ds, sizeof(DevState), cudaMemcpyDeviceToHost, stream));
+        PS_CUDA_TRY(err, cudaEventRecord(ev_rb, stream));
+        return PS_OK;
+    }
+    // ... and the sub-step's one host synchronisation: on those copies only, not on what was queued after them
+    int stage_build_wait() {
+        int rc;
+        PS_CUDA_TRY(err, cudaEventSynchronize(ev_rb));
+        if ((rc = check_host_copy())) return rc;
         h_step = hc->sd;
         r0_step = hc->ds.rounds_last + 1;
         // PS_SLAB_FORCE_LATE=1 (tests): behave as if the right boundary always depended on the left one
@@ -833,15 +853,16 @@ struct SlabCollider {
     }
 
     // stage 3 (recv_l holds the left rank's M1): take over the boundary states, unblock, phase B
-    int stage_phase_b() {
+    int stage_phase_b(uint32_t r0) {
         cudaStream_t st = stream;
         slab_unpack_kernel<Real><<<(g.cap_h + 255) / 256, 256, 0, st>>>(in_m1, rec[cur ^ 1], &sd->zero, &sd->c_first2, g.cap_h, sd);
-        slab_unblock_kernel<<<(h_step.c_first2 + 255) / 256 + 1, 256, 0, st>>>(head, brem, wl[r0_step % 3], &ds->wl_count[r0_step % 3], r0_step, sd);
+        slab_unblock_kernel<<<(2 * g.cap_h + 255) / 256 + 1, 256, 0, st>>>(head, brem, wl[0], wl[1], wl[2], ds, r0, sd);   // two columns of slots at most
         launches += 2;
         if (int d = dbg("unpack+unblock")) return d;
-        if (int rc = launch_resolve(k_step, r0_step)) return rc;
+        if (int rc = launch_resolve(k_step, r0)) return rc;
         return dbg("resolve B");
     }
+    int stage_phase_b() { return stage_phase_b(r0_step); }
 
     // stage 4: finish the sub-step (the new layout becomes current)
     int stage_finish() {
@@ -891,7 +912,12 @@ struct SlabCollider {
             in_r = p2p_r ? x_msg(xbuf, X_M0_FROM_RIGHT + par) : recv_r;
         }
         tick(2);
-        if ((rc = stage_build())) return rc;
+        if ((rc = stage_build_queue())) return rc;
+        // With one-sided transport on every boundary of this rank nothing that follows needs a decision of the host (the device
+        // picks the early or late hand-over, phase B continues from the round phase A ended with): the rest of the sub-step is
+        // queued first and the host looks at the mid-step counters afterwards, while the GPU is busy with the hand-over.
+        const bool queue_ahead = (!g.gl || p2p_l) && (!g.gr || p2p_r) && !debug_sync;
+        if (!queue_ahead && (rc = stage_build_wait())) return rc;
         tick(5);
         const bool send_now = send_now_step;
         if (g.gr && p2p_r) {
@@ -911,7 +937,7 @@ struct SlabCollider {
         }
         in_m1 = p2p_l ? x_msg(xbuf, X_M1 + par) : recv_l;
         tick(6);
-        if (g.gl && (rc = stage_phase_b())) return rc;
+        if (g.gl && (rc = stage_phase_b(queue_ahead ? RESOLVE_CONTINUE : r0_step))) return rc;
         tick(7);
         if (g.gr && p2p_r) {
             if ((rc = pack_m1())) return rc;
@@ -920,6 +946,7 @@ struct SlabCollider {
             if ((rc = pack_m1())) return rc;
             if ((rc = nccl_try(api.Send(send_r, hb, kNcclUint8, rank + 1, comm, st), "ncclSend (late M1)"))) return rc;
         }
+        if (queue_ahead && (rc = stage_build_wait())) return rc;
         rc = stage_finish();
         tick(8);
         tock();
