@@ -478,7 +478,7 @@ def run_ours(args):
         config = workload_config(args, prec)
         if collide:
             # the headline numbers of the collision scenes again, where the driver keeps the whole object
-            for key in ("collide_256Mi", "collide_16Mi"):
+            for key in ("collide_256Mi", "collide_16Mi", "collide_16Mi_f64"):
                 if key in collide and "error" not in collide[key]:
                     c = collide[key]
                     config[key] = {k: c.get(k) for k in ("updates_per_s", "ms_per_substep", "pairs", "rounds", "n_gpus", "scaling",
@@ -650,9 +650,44 @@ def collide_block(torch, dist, args, rank, world, local):
                 blk = time_collision_scene(torch, None, c, cs, frames, 2, 1, prec, local)
                 blk["workload"] = "16Mi particles, full updatePhysics with uniform-grid collisions (BASELINE.json configs[3]), fp32, one GPU"
                 out["collide_16Mi"] = blk
+            # the same scene in core.zig's own arithmetic (f64 records: twice the bytes)
+            with Simulation(cs, precision="f64", collisions=True, device=local) as c:
+                c.spawn(1)
+                blk = time_collision_scene(torch, None, c, cs, frames, 2, 1, "f64", local)
+                blk["workload"] = "16Mi particles, full updatePhysics with collisions, f64 (core.zig as written), one GPU"
+                out["collide_16Mi_f64"] = blk
         except Exception as e:  # noqa: BLE001
-            out["collide_16Mi"] = {"error": f"{type(e).__name__}: {e}"}
+            out.setdefault("collide_16Mi", {"error": f"{type(e).__name__}: {e}"})
+            out.setdefault("collide_16Mi_f64", {"error": f"{type(e).__name__}: {e}"})
+        # like for like on the collision path: 1 Mi particles, 24 sub-steps, f64, the CPU port (one thread) against one GPU
+        try:
+            out["cpu_vs_gpu_collide_1Mi_f64"] = cpu_vs_gpu_collide(torch, local)
+        except Exception as e:  # noqa: BLE001
+            out["cpu_vs_gpu_collide_1Mi_f64"] = {"error": f"{type(e).__name__}: {e}"}
     return out
+
+
+def cpu_vs_gpu_collide(torch, local, n=1 << 20, substeps=24):
+    """BASELINE.md run B4 inside the line: full updatePhysics with collisions, f64, oracle/core_ref.hpp on one thread against
+    libparticles_cuda (device-resident), same initial state, final states compared bit for bit."""
+    import oracle   # checker + CPU baseline of this case only
+    from particle_simulator_b200 import Simulation, scenes
+
+    sc = scenes.scaled_scene(n)
+    pos0, vel0 = scenes.spawn(sc, seed=1, dtype=np.float64)
+    p, v = pos0.copy(), vel0.copy()
+    params = oracle.make_params(radius=sc.radius, width=sc.width, height=sc.height, grid_size=sc.grid_size)
+    secs = oracle.run(params, p, v, substeps, collisions=True)["seconds"]
+    with Simulation(sc, precision="f64", collisions=True, device=local) as c:
+        c.set_stream(torch.cuda.current_stream().cuda_stream)
+        c.upload(pos0, vel0)
+        c.step_substeps(8)                      # warm-up
+        c.upload(pos0, vel0)
+        ms = timed(torch, None, lambda: c.step_substeps(substeps), 1)
+        gp, gv = c.download(dtype=np.float64)
+    same = bool(np.array_equal(gp.view(np.uint8), p.view(np.uint8)) and np.array_equal(gv.view(np.uint8), v.view(np.uint8)))
+    return {"particles": n, "substeps": substeps, "dtype": "f64", "cpu_port_updates_per_s": n * substeps / secs, "cpu_cores": 1,
+            "gpu_updates_per_s": n * substeps / (ms * 1e-3), "speedup_vs_cpu_port": secs * 1e3 / ms, "bit_identical": same}
 
 
 def gravity_pile(torch, local, settle_frames=100, timed_frames=25):
