@@ -218,8 +218,10 @@ int ps_compute_start_array_static(const uint32_t* grid_array, uint32_t* start_ar
 /* ---- one scene across the GPUs of one box (collision scenes) ------------------------
  * No counterpart in the reference (single process, single thread).  One process per GPU; rank k owns
  * the particles whose grid column (src/core.zig:104) lies in its slab of whole cell columns and
- * exchanges migrants, a one-column halo and the boundary particles' states with its x-neighbours by
- * NCCL send/recv.  Results are those of ps_step on one GPU, bit for bit.  `cfg` describes the WHOLE
+ * exchanges migrants, a one-column halo and the boundary particles' states with its x-neighbours: by direct
+ * stores into the neighbour's receive buffers over NVLink where the two processes can map each other's memory
+ * (CUDA IPC; the usual case on one box), by NCCL send/recv otherwise (PS_SLAB_TRANSPORT=nccl forces that; the
+ * communicator is always needed for the set-up).  Results are those of ps_step on one GPU, bit for bit.  `cfg` describes the WHOLE
  * scene (count = all particles) on every rank; cfg->collisions must be 1. */
 typedef struct ps_slab ps_slab;
 /* ncclGetUniqueId: rank 0 calls it and hands the 128 bytes to every rank (any host-side channel). */
