@@ -798,6 +798,46 @@ __device__ __forceinline__ int resolve_item(Rec<Real>* rec, const uint32_t* __re
     return (more_a ? 1 : 0) + (more_b ? 1 : 0);
 }
 
+// The same work item for the tail rounds (one CTA, lists of a few dozen items, hundreds of rounds in a row): there the cost
+// of a round is the dependent instruction chain of ONE warp, and every early exit above is a point where the warp splits and
+// runs its pieces one after the other.  This version has no exits: every lane loads, tests and computes; one predicate decides
+// who stores.  (Loads of a lane that will not run are harmless: every address is inside the arrays.)
+template <class Real>
+__device__ __forceinline__ int resolve_item_tail(Rec<Real>* rec, const uint32_t* __restrict__ chunks, const uint32_t* __restrict__ pool,
+                                                 unsigned long long* head, uint2 item, uint32_t r, const StepConst<Real>& k, uint2 (&next)[2]) {
+    const uint32_t a = item.x, ea = item.y;
+    const uint32_t b = ea & ENT_SLOT_MASK;
+    const unsigned long long ha = head[a], hb = head[b];
+    const Rec<Real> Ra = ld_rec(rec + a), Rb = ld_rec(rec + b);
+    const uint32_t wa = head_low(ha), wb = head_low(hb);
+    const uint32_t pos_a = head_pos(ha), pos_b = head_pos(hb);
+    // the words that hold the next entries when the lists go on inside their chunks (entry pos + 1 sits at chunk word pos)
+    const uint32_t ca = chunks[(size_t)a * LIST_CHUNK + (pos_a < LIST_CHUNK - 1u ? pos_a : LIST_CHUNK - 1u)];
+    const uint32_t cb = chunks[(size_t)b * LIST_CHUNK + (pos_b < LIST_CHUNK - 1u ? pos_b : LIST_CHUNK - 1u)];
+    const bool go = !(r == 0u && b < a) && head_stamp(ha) != r + 1 && head_stamp(hb) != r + 1 && (wb & HEAD_LIVE) != 0u &&
+                    (wb & ENT_SLOT_MASK) == a && ((wb ^ ea) & ENT_CENTRE) != 0u && !(b < a && head_stamp(hb) == r);
+    const bool more_a = go && !(wa & ENT_LAST), more_b = go && !(wb & ENT_LAST);
+    uint32_t na = ca, nb = cb;
+    // lists longer than nine entries continue in the pool (rare: take the general path)
+    if (more_a && (wa & HEAD_OVF) && pos_a >= LIST_CHUNK - 1u) na = load_entry(chunks, pool, a, pos_a + 1u, 1u);
+    if (more_b && (wb & HEAD_OVF) && pos_b >= LIST_CHUNK - 1u) nb = load_entry(chunks, pool, b, pos_b + 1u, 1u);
+    na = more_a ? (na | HEAD_LIVE | (wa & HEAD_OVF)) : 0u;
+    nb = more_b ? (nb | HEAD_LIVE | (wb & HEAD_OVF)) : 0u;
+    const bool a_centre = (ea >> ENT_ROLE_BIT) & 1u;
+    Rec<Real> I = a_centre ? Rb : Ra, J = a_centre ? Ra : Rb;
+    resolve_pair<Real>(I, J, k);
+    if (go) {
+        st_rec(rec + (a_centre ? b : a), I);
+        st_rec(rec + (a_centre ? a : b), J);
+        head[a] = head_word(r + 1, pos_a + 1u, na);
+        head[b] = head_word(r + 1, pos_b + 1u, nb);
+    }
+    const uint2 ia = make_uint2(a, na), ib = make_uint2(b, nb);
+    next[0] = more_a ? ia : ib;
+    next[1] = ib;
+    return (more_a ? 1 : 0) + (more_b ? 1 : 0);
+}
+
 // One round over the work list `wl[0..cnt)` by one or many CTAs; appends the particles advanced in this round, with
 // their new head entry, to `out` (buffered per CTA: one global atomic per batch of 256 items).
 template <class Real>
@@ -958,7 +998,11 @@ resolve_kernel(Rec<Real>* rec, const uint32_t* __restrict__ chunks, const uint32
         for (uint32_t idx = threadIdx.x; idx < cnt; idx += RESOLVE_TAIL_THREADS) {
             uint2 next[2];
             PS_MARK(1);
+#ifdef PS_TAIL_BRANCHY
             const int m = resolve_item<Real, true>(rec, chunks, pool, head, in[idx], r, k, next PS_PROF_ARG);
+#else
+            const int m = resolve_item_tail<Real>(rec, chunks, pool, head, in[idx], r, k, next);
+#endif
             if (m) {                                         // (a shared-memory atomic per executed pair: no warp-wide vote, lanes stay independent)
                 const uint32_t at = atomicAdd(&tl_n[nxt], (uint32_t)m);
                 out[at] = next[0];
