@@ -73,8 +73,12 @@ typedef struct ps_config {
                                    BASELINE.json's integration configs name; the reference has no such switch */
     uint32_t fuse_substeps;     /* integrate-only scenes: advance up to this many sub-steps per kernel pass in
                                    registers (bit-identical; 0 or 1 = one pass per sub-step, the roofline run) */
-    uint32_t contacts_per_particle; /* capacity of the contact list, entries per particle (0 = default 12) */
-    uint64_t reserved[4];
+    uint32_t contacts_per_particle; /* capacity of the contact lists' overflow pool, entries per particle (0 = default 12) */
+    uint64_t slab_capacity_percent; /* ps_slab_* only: particles one rank can hold, in percent of the average share
+                                       count / nranks (0 = default 125, sized for near-uniform scenes; a scene that piles up
+                                       in some slabs needs more, up to 100 * nranks; scenes of at most 4 Mi particles always
+                                       get room for all of them); too little is reported as PS_ERR_CAPACITY */
+    uint64_t reserved[3];
 } ps_config;
 
 typedef struct ps_stats {

@@ -44,7 +44,8 @@ class PsConfig(ctypes.Structure):
         ("collisions", ctypes.c_int32),
         ("fuse_substeps", ctypes.c_uint32),
         ("contacts_per_particle", ctypes.c_uint32),
-        ("reserved", ctypes.c_uint64 * 4),
+        ("slab_capacity_percent", ctypes.c_uint64),
+        ("reserved", ctypes.c_uint64 * 3),
     ]
 
 

@@ -371,7 +371,7 @@ class SlabSimulation:
     on rank 0, handed to all ranks by the host program (torch.distributed broadcast, a file, ...)."""
 
     def __init__(self, scene: scenes.Scene, rank: int, nranks: int, nccl_id: bytes | None = None, *, precision: str = "f64",
-                 device: int = 0, contacts_per_particle: int = 0):
+                 device: int = 0, contacts_per_particle: int = 0, capacity_percent: int = 0):
         self._L = capi.load()
         cfg = capi.PsConfig()
         cfg.struct_size = ctypes.sizeof(capi.PsConfig)
@@ -383,6 +383,7 @@ class SlabSimulation:
         cfg.precision = capi.PS_F64 if precision == "f64" else capi.PS_F32
         cfg.collisions = 1
         cfg.contacts_per_particle = contacts_per_particle
+        cfg.slab_capacity_percent = capacity_percent
         self.cfg, self.scene, self.rank, self.nranks = cfg, scene, rank, nranks
         h = ctypes.c_void_p()
         idbuf = ctypes.create_string_buffer(nccl_id, 128) if nccl_id is not None else None
@@ -492,7 +493,8 @@ class SlabGroup:
     """All ranks of a slab-decomposed scene emulated in one process on one GPU (ps_slabgroup_*): the multi-rank
     protocol with device copies instead of NCCL.  For tests and for boxes with fewer GPUs than slabs."""
 
-    def __init__(self, scene: scenes.Scene, nranks: int, *, precision: str = "f64", device: int = 0, contacts_per_particle: int = 0):
+    def __init__(self, scene: scenes.Scene, nranks: int, *, precision: str = "f64", device: int = 0, contacts_per_particle: int = 0,
+                 capacity_percent: int = 0):
         self._L = capi.load()
         cfg = capi.PsConfig()
         cfg.struct_size = ctypes.sizeof(capi.PsConfig)
@@ -504,6 +506,7 @@ class SlabGroup:
         cfg.precision = capi.PS_F64 if precision == "f64" else capi.PS_F32
         cfg.collisions = 1
         cfg.contacts_per_particle = contacts_per_particle
+        cfg.slab_capacity_percent = capacity_percent
         self.scene, self.nranks = scene, nranks
         h = ctypes.c_void_p()
         rc = self._L.ps_slabgroup_create(ctypes.byref(cfg), nranks, ctypes.byref(h))

@@ -555,7 +555,8 @@ struct SlabCollider {
         g.xlo = rank > 0 ? (uint32_t)(((uint64_t)(rank - 1) * cols) / nranks) : 0u;
         g.xhi = rank < nranks - 1 ? (uint32_t)(((uint64_t)(rank + 2) * cols) / nranks) : cols;
         const uint64_t share = (n_total + nranks - 1) / nranks;
-        uint64_t cap = n_total <= (4u << 20) ? n_total : share + share / 4 + 16ull * rows + 4096;
+        const uint64_t pct = c.slab_capacity_percent ? c.slab_capacity_percent : 125;
+        uint64_t cap = n_total <= (4u << 20) ? n_total : share * pct / 100 + 16ull * rows + 4096;
         if (cap > n_total) cap = n_total;
         if (cap < 16) cap = 16;
         g.cap = (uint32_t)cap;

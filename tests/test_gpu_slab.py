@@ -130,6 +130,35 @@ def test_emulated_ranks_dense_band_under_gravity(nranks, precision):
     assert max(counts) > 3 * (scene.count // nranks) // 2, "the scene was meant to be unbalanced"
 
 
+def test_slab_capacity_is_configurable():
+    """Above 4 Mi particles a rank is sized for 1.25 x the average share (ps_config.slab_capacity_percent = 0).  A scene with
+    nine tenths of its particles in one rank's slab is refused with PS_ERR_CAPACITY at that size, and runs, bit-identical to the
+    oracle, once the caller asks for room."""
+    from particle_simulator_b200 import SlabGroup, capi
+
+    n = 5_000_000
+    scene = scenes.scaled_scene(n)
+    rng = np.random.default_rng(21)
+    pos = np.empty((n, 2))
+    left = rng.random(n) < 0.9
+    pos[:, 0] = np.where(left, rng.uniform(scene.radius, scene.width * 0.45, n), rng.uniform(scene.width * 0.55, scene.width - scene.radius, n))
+    pos[:, 1] = rng.uniform(scene.radius, scene.height - scene.radius, n)
+    vel = rng.uniform(-640.0, 640.0, size=(n, 2))
+    with pytest.raises(capi.PsError) as e:
+        with SlabGroup(scene, 2, precision="f32") as g:
+            g.upload_global(pos, vel)
+    assert e.value.status == capi.PS_ERR_CAPACITY
+    want_p, want_v, out = run_oracle(scene, pos.astype(np.float32), vel.astype(np.float32), 2, collisions=True)
+    with SlabGroup(scene, 2, precision="f32", capacity_percent=200, contacts_per_particle=24) as g:
+        g.upload_global(pos, vel)
+        g.step_substeps(2)
+        parts = [g.download_owned(r) for r in range(2)]
+    got_p, got_v = gather(parts, n, np.float32)
+    assert_bit_exact(got_p, want_p, "positions")
+    assert_bit_exact(got_v, want_v, "velocities")
+    assert len(parts[0][0]) > 4_000_000
+
+
 def _two_rank_worker(rank, world, port, tmpdir, case):
     import torch
     import torch.distributed as dist
