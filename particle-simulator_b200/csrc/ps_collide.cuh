@@ -20,19 +20,18 @@
 //   move     computeSortedArray (:145-159): rank each particle among its cell's indices (ascending
 //            index = what the reference's stable counting sort produces) and write its integrated
 //            record and index to slot cell_start + rank of the other buffer
-//   detect   every slot walks its 3x3 cell block in a FIXED segment order that visits its contacts
-//            exactly in the order the reference's pair list (:164-209) mentions that particle.  The
-//            position of an entry in the global list is the lexicographic key (centre slot, offset
-//            index, neighbour slot), so each particle's own sub-list is produced without
-//            materialising or sorting the global list.  One kernel: every candidate tested once, the
-//            hits kept as a bit mask; CTA scan + one atomic per CTA reserves list space; the mask is
-//            replayed in list order.
+//   detect   every slot tests the candidates of its 3x3 cell block once; the hits, as a bit mask, are permuted into the
+//            order in which the reference's pair list (:164-209) mentions that particle.  The position of an entry in
+//            the global list is the lexicographic key (centre slot, offset index, neighbour slot), so each particle's
+//            own sub-list is produced without materialising or sorting the global list.  Entry 0 goes into the
+//            particle's 64-bit head word, entries 1-8 into its own chunk at a fixed place: nothing is reserved or
+//            scanned.  Warp-autonomous, two phases (all slots; then only the third that hit something, compacted).
 //   resolve  a pair may run as soon as it heads BOTH of its particles' sub-lists: pairs that share
 //            no particle commute, so executing all such "ready" pairs together, round after round,
 //            is bit-identical to the sequential loop.  One persistent cooperative kernel runs the
 //            rounds (one grid barrier each) over work lists that hold only the particles whose head
 //            changed in the previous round, so total work is O(pairs).  Short lists are finished by
-//            one CTA, the shortest out of shared memory and L1 (deep chains = many short rounds).
+//            one CTA out of shared memory, one CTA barrier per round (deep chains = many short rounds).
 #pragma once
 #include <cooperative_groups.h>
 
