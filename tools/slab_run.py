@@ -36,6 +36,7 @@ def main():
     ap.add_argument("--gravity", action="store_true")
     ap.add_argument("--check", action="store_true", help="compare with the oracle (small scenes)")
     ap.add_argument("--spawn-on-device", action="store_true")
+    ap.add_argument("--dense-band", action="store_true", help="non-uniform scene: the default 720x640 world with 80 %% of --particles in a band astride a slab boundary")
     ap.add_argument("--seed", type=int, default=1)
     ap.add_argument("--hang-dump", type=int, default=90)
     ap.add_argument("--verbose", action="store_true")
@@ -46,6 +47,17 @@ def main():
     if world > 1:
         dist.init_process_group("gloo")          # host-side channel: the NCCL id and the result gather only
     scene = scenes.scaled_scene(args.particles) if not args.width else scenes.Scene(count=args.particles, width=args.width, height=args.height)
+    band = None
+    if args.dense_band:
+        scene = scenes.default_scene().with_(count=args.particles)
+        rng = np.random.default_rng(args.seed)
+        n = args.particles
+        bp = np.empty((n, 2))
+        bv = rng.uniform(-200.0, 200.0, size=(n, 2))
+        in_band = rng.random(n) < 0.8
+        bp[:, 0] = np.where(in_band, np.clip(rng.normal(180.0, 25.0, n), scene.radius, scene.width - scene.radius), rng.uniform(scene.radius, scene.width, n))
+        bp[:, 1] = rng.uniform(scene.radius, scene.height, n)
+        band = (np.ascontiguousarray(bp), np.ascontiguousarray(bv))
     idt = torch.zeros(128, dtype=torch.uint8)
     if world > 1:
         if rank == 0:
@@ -53,10 +65,13 @@ def main():
         dist.broadcast(idt, 0)
     log(rank, "creating slab handle", scene)
     sim = SlabSimulation(scene, rank, world, bytes(idt.numpy().tobytes()) if world > 1 else None, precision=args.precision,
-                         device=local, contacts_per_particle=24)
+                         device=local, contacts_per_particle=96 if args.dense_band else 24)
     log(rank, "columns", sim.columns())
     pos0 = vel0 = None
-    if args.spawn_on_device:
+    if band is not None:
+        pos0, vel0 = band
+        sim.upload_global(pos0, vel0)
+    elif args.spawn_on_device:
         sim.spawn(args.seed)
     else:
         pos0, vel0 = scenes.spawn(scene, seed=args.seed)
