@@ -788,8 +788,13 @@ __device__ __forceinline__ int resolve_item(Rec<Real>* rec, const uint32_t* __re
     PS_KEEP(I.u); PS_KEEP(J.u); PS_KEEP(I.x); PS_MARK(6);
     st_rec(rec + (a_centre ? b : a), I);
     st_rec(rec + (a_centre ? a : b), J);
-    head[a] = head_word(r + 1, pos_a + 1u, na);
-    head[b] = head_word(r + 1, pos_b + 1u, nb);
+    // A particle whose sub-list ends with this pair is never looked at again in this sub-step (every partner's entry for it
+    // has been consumed together with its own), and the tie-break above rests on stamps written before this round: its head
+    // word need not be written.  The long rounds are bound by these small scattered stores, four per pair (measured:
+    // fewer or wider loads, more loads in flight change nothing; dropping this one takes 12 % off the kernel).  Slab
+    // handles keep the store for the last two local columns: slab_right_check_kernel reads their LIVE bits.
+    if (LOCAL || more_a || a >= k.keep_from) head[a] = head_word(r + 1, pos_a + 1u, na);
+    if (LOCAL || more_b || b >= k.keep_from) head[b] = head_word(r + 1, pos_b + 1u, nb);
     PS_MARK(7);
     const uint2 ia = make_uint2(a, na), ib = make_uint2(b, nb);     // (constant indices keep `next` in registers)
     next[0] = more_a ? ia : ib;
@@ -912,8 +917,9 @@ __device__ __forceinline__ void resolve_round_warps(Rec<Real>* rec, const uint32
 template <class Real>
 __global__ void __launch_bounds__(RESOLVE_THREADS)
 resolve_kernel(Rec<Real>* rec, const uint32_t* __restrict__ chunks, const uint32_t* __restrict__ pool, unsigned long long* head,
-               uint2* wl0, uint2* wl1, uint2* wl2, StepConst<Real> k, DevState* ds, uint32_t r_start) {
+               uint2* wl0, uint2* wl1, uint2* wl2, StepConst<Real> k, DevState* ds, uint32_t r_start, const uint32_t* keep_from) {
     cg::grid_group grid = cg::this_grid();
+    k.keep_from = keep_from ? *keep_from : 0xffffffffu;
     __shared__ uint2 sh_buf[(RESOLVE_THREADS / 32) * RESOLVE_WBUF];   // grid phase: one append buffer per warp; tail: one for the CTA
     __shared__ uint32_t sh_cnt, sh_base;
     auto list = [&](uint32_t i) { return i == 0 ? wl0 : (i == 1 ? wl1 : wl2); };   // (an indexed array would live in local memory)
@@ -1181,8 +1187,8 @@ struct Collider {
         {
             Rec<Real>* a_rec = rec[nw]; const uint32_t* a_chunks = chunks; const uint32_t* a_ent = entries;
             unsigned long long* a_head = head; uint2 *a0 = wl[0], *a1 = wl[1], *a2 = wl[2];
-            StepConst<Real> a_k = k; DevState* a_ds = ds; uint32_t a_r0 = 0;
-            void* args[] = {&a_rec, &a_chunks, &a_ent, &a_head, &a0, &a1, &a2, &a_k, &a_ds, &a_r0};
+            StepConst<Real> a_k = k; DevState* a_ds = ds; uint32_t a_r0 = 0; const uint32_t* a_keep = nullptr;
+            void* args[] = {&a_rec, &a_chunks, &a_ent, &a_head, &a0, &a1, &a2, &a_k, &a_ds, &a_r0, &a_keep};
             const uint64_t want = (n + RESOLVE_THREADS - 1) / RESOLVE_THREADS;
             const unsigned grid = (unsigned)(want < (uint64_t)resolve_grid ? want : (uint64_t)resolve_grid);
             PS_CUDA_TRY(err, cudaLaunchCooperativeKernel((const void*)resolve_kernel<Real>, dim3(grid), dim3(RESOLVE_THREADS), args, 0, st));

@@ -33,6 +33,8 @@ struct StepConst {
     int gs_pow2;
     uint32_t rows, cols;
     int t_acc;
+    uint32_t keep_from;   // resolve: slots from here on get their head word written even when their sub-list has ended (slab handles: the
+                          // two boundary columns that slab_right_check_kernel inspects); 0xffffffff on a single GPU.  Set inside the kernel.
 };
 
 template <class Real>

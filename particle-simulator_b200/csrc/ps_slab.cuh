@@ -737,7 +737,8 @@ struct SlabCollider {
     int launch_resolve(const StepConst<Real>& k, uint32_t r0) {
         Rec<Real>* a_rec = rec[cur ^ 1]; const uint32_t* a_chunks = chunks; const uint32_t* a_ent = entries; unsigned long long* a_head = head;
         uint2 *a0 = wl[0], *a1 = wl[1], *a2 = wl[2]; StepConst<Real> a_k = k; DevState* a_ds = ds; uint32_t a_r0 = r0;
-        void* args[] = {&a_rec, &a_chunks, &a_ent, &a_head, &a0, &a1, &a2, &a_k, &a_ds, &a_r0};
+        const uint32_t* a_keep = &sd->c_last2;        // finished sub-lists of the last two local columns keep their head words current
+        void* args[] = {&a_rec, &a_chunks, &a_ent, &a_head, &a0, &a1, &a2, &a_k, &a_ds, &a_r0, &a_keep};
         const uint64_t want = ((uint64_t)g.cap + RESOLVE_THREADS - 1) / RESOLVE_THREADS;
         const unsigned grid = (unsigned)(want < (uint64_t)resolve_grid ? want : (uint64_t)resolve_grid);
         PS_CUDA_TRY(err, cudaLaunchCooperativeKernel((const void*)resolve_kernel<Real>, dim3(grid), dim3(RESOLVE_THREADS), args, 0, stream));

@@ -65,6 +65,7 @@ def run_rounds(lists, execute, rng):
     # detect_kernel: on the first list only if the first partner has a higher slot (round 0 runs pairs from the lower slot)
     work = [(a, lists[a][0]) for a in range(n) if lists[a] and lists[a][0][0] > a]
     r, executed = 0, 0
+    done = [0] * n
     while work:
         rng.shuffle(work)                                        # threads of one round run in no particular order
         nxt = []
@@ -85,15 +86,21 @@ def run_rounds(lists, execute, rng):
             nb = None if last_b else load_entry(chunks, pool, b, pos_b + 1, ovf_b)
             execute(b, a) if a_centre else execute(a, b)
             executed += 1
-            head[a] = [r + 1, pos_a + 1, na is not None, ovf_a, bool(na and na[1]), na[0] if na else None]
-            head[b] = [r + 1, pos_b + 1, nb is not None, ovf_b, bool(nb and nb[1]), nb[0] if nb else None]
+            # a finished sub-list's head word is NOT written back (nobody looks at that particle again in this sub-step,
+            # and the tie-break rests on stamps of earlier rounds): the stale word must do no harm
+            done[a] += 1
+            done[b] += 1
+            if na:
+                head[a] = [r + 1, pos_a + 1, True, ovf_a, na[1], na[0]]
+            if nb:
+                head[b] = [r + 1, pos_b + 1, True, ovf_b, nb[1], nb[0]]
             if na:
                 nxt.append((a, na[0]))
             if nb:
                 nxt.append((b, nb[0]))
         work = nxt
         r += 1
-    assert all(not h[2] and h[1] == len(l) for h, l in zip(head, lists)), "some sub-list was not drained"
+    assert all(d == len(l) for d, l in zip(done, lists)), "some sub-list was not drained"
     return r, executed
 
 
